@@ -1,0 +1,629 @@
+// build.cu -- on-device acceleration-structure build for sm_100a.
+//
+// Replaces the reference's createGaussianParticlesBVH / createGAS / createIAS / optixAccelBuild
+// (src/GaussianTracer.cpp:297-473): there the host loops over N particles building 80-byte OptixInstance
+// records and OptiX builds a two-level BVH on RT-core hardware.  B200 has no RT cores, so this file builds a
+// software BVH entirely on the device:
+//   proxy boxes -> 63-bit Morton codes -> hand-written LSD radix sort (no CUB/Thrust) -> Karras 2012
+//   binary hierarchy -> bottom-up atomic refit -> level-synchronous collapse into 8-wide nodes whose
+//   leaf children are runs of <= LEAF_MAX Morton-consecutive records.
+// All kernels are one-time (per scene) and HBM-bound streaming passes; none is on the per-frame path.
+#include <cfloat>
+#include <cstdio>
+#include <vector>
+
+#include "grt_internal.h"
+
+namespace grt {
+
+#define CK(x)                              \
+    do {                                   \
+        cudaError_t e_ = (x);              \
+        if (e_ != cudaSuccess) return (int)e_; \
+    } while (0)
+
+static inline unsigned int cdiv(unsigned long long a, unsigned int b) { return (unsigned int)((a + b - 1) / b); }
+
+// ------------------------------------------------------------------------------------------- radix sort
+constexpr int RS_THREADS = 256;
+constexpr int RS_ITEMS = 16;
+constexpr int RS_TILE = RS_THREADS * RS_ITEMS;
+constexpr int RS_WARPS = RS_THREADS / 32;
+
+__global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const uint64_t* __restrict__ keys, uint32_t n, int shift,
+                                                             uint32_t* __restrict__ ghist, uint32_t nblocks) {
+    __shared__ uint32_t h[256];
+    const uint32_t tid = threadIdx.x;
+    h[tid] = 0;
+    __syncthreads();
+    const uint64_t base = (uint64_t)blockIdx.x * RS_TILE;
+#pragma unroll 4
+    for (int r = 0; r < RS_ITEMS; ++r) {
+        uint64_t i = base + (uint64_t)r * RS_THREADS + tid;
+        if (i < n) atomicAdd(&h[(uint32_t)(keys[i] >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    ghist[(uint64_t)tid * nblocks + blockIdx.x] = h[tid];
+}
+
+// exclusive scan of `total` counters in place, one block of 1024 threads
+__global__ void __launch_bounds__(1024) rs_scan_kernel(uint32_t* __restrict__ data, uint32_t total) {
+    __shared__ uint32_t sums[1024];
+    const uint32_t tid = threadIdx.x;
+    const uint32_t chunk = (total + 1023u) / 1024u;
+    const uint32_t b = tid * chunk;
+    const uint32_t e = min(b + chunk, total);
+    uint32_t s = 0;
+    for (uint32_t i = b; i < e; ++i) s += data[i];
+    sums[tid] = s;
+    __syncthreads();
+    // Hillis-Steele inclusive scan over 1024 partial sums
+    for (uint32_t off = 1; off < 1024; off <<= 1) {
+        uint32_t v = (tid >= off) ? sums[tid - off] : 0u;
+        __syncthreads();
+        sums[tid] += v;
+        __syncthreads();
+    }
+    uint32_t run = sums[tid] - s;  // exclusive prefix of this chunk
+    for (uint32_t i = b; i < e; ++i) {
+        uint32_t v = data[i];
+        data[i] = run;
+        run += v;
+    }
+}
+
+__global__ void __launch_bounds__(RS_THREADS) rs_scatter_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                                                                uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
+                                                                uint32_t n, int shift, const uint32_t* __restrict__ ghist, uint32_t nblocks) {
+    __shared__ uint32_t running[256];
+    __shared__ uint32_t cnt[RS_WARPS][256];
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    running[tid] = ghist[(uint64_t)tid * nblocks + blockIdx.x];
+#pragma unroll
+    for (int w = 0; w < RS_WARPS; ++w) cnt[w][tid] = 0;
+    __syncthreads();
+    const uint64_t base = (uint64_t)blockIdx.x * RS_TILE;
+    for (int r = 0; r < RS_ITEMS; ++r) {
+        const uint64_t i = base + (uint64_t)r * RS_THREADS + tid;
+        const bool valid = i < n;
+        uint64_t key = 0;
+        uint32_t val = 0;
+        if (valid) { key = keys_in[i]; val = vals_in[i]; }
+        // invalid lanes get a private pseudo-digit so they only match themselves
+        const uint32_t dgt = valid ? ((uint32_t)(key >> shift) & 255u) : (256u + lane);
+        const uint32_t peers = __match_any_sync(0xFFFFFFFFu, dgt);
+        const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
+        if (valid && rank == 0) cnt[warp][dgt] = __popc(peers);
+        __syncthreads();
+        if (valid) {
+            uint32_t pos = running[dgt] + rank;
+            for (uint32_t w = 0; w < warp; ++w) pos += cnt[w][dgt];
+            keys_out[pos] = key;
+            vals_out[pos] = val;
+        }
+        __syncthreads();
+        uint32_t sum = 0;
+#pragma unroll
+        for (int w = 0; w < RS_WARPS; ++w) { sum += cnt[w][tid]; cnt[w][tid] = 0; }
+        running[tid] += sum;
+        __syncthreads();
+    }
+}
+
+int radix_sort_pairs(uint64_t* d_keys, uint64_t* d_keys_tmp, uint32_t* d_vals, uint32_t* d_vals_tmp, uint32_t n,
+                     cudaStream_t stream, unsigned long long* launches, bool* result_in_tmp) {
+    *result_in_tmp = false;
+    if (n == 0) return 0;
+    const uint32_t nblocks = cdiv(n, RS_TILE);
+    uint32_t* d_hist = nullptr;
+    CK(cudaMalloc(&d_hist, sizeof(uint32_t) * 256ull * nblocks));
+    uint64_t* kin = d_keys; uint64_t* kout = d_keys_tmp;
+    uint32_t* vin = d_vals; uint32_t* vout = d_vals_tmp;
+    for (int pass = 0; pass < 8; ++pass) {
+        const int shift = pass * 8;
+        rs_hist_kernel<<<nblocks, RS_THREADS, 0, stream>>>(kin, n, shift, d_hist, nblocks);
+        rs_scan_kernel<<<1, 1024, 0, stream>>>(d_hist, 256u * nblocks);
+        rs_scatter_kernel<<<nblocks, RS_THREADS, 0, stream>>>(kin, vin, kout, vout, n, shift, d_hist, nblocks);
+        *launches += 3;
+        std::swap(kin, kout);
+        std::swap(vin, vout);
+    }
+    // 8 passes: the result is back in the original buffers
+    cudaError_t e = cudaStreamSynchronize(stream);
+    cudaFree(d_hist);
+    if (e != cudaSuccess) return (int)e;
+    CK(cudaGetLastError());
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------- bounds + Morton
+__device__ __forceinline__ uint32_t enc_f(float f) {
+    uint32_t b = __float_as_uint(f);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__host__ __device__ __forceinline__ float dec_f(uint32_t e) {
+    uint32_t b = (e & 0x80000000u) ? (e & 0x7FFFFFFFu) : ~e;
+#ifdef __CUDA_ARCH__
+    return __uint_as_float(b);
+#else
+    float f; memcpy(&f, &b, 4); return f;
+#endif
+}
+
+// bounds[0..2] = encoded min of box centres, bounds[3..5] = encoded max, bounds[6] = live count
+__global__ void bounds_kernel(const float4* __restrict__ lo, const float4* __restrict__ hi, uint32_t n, uint32_t* __restrict__ bounds) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    float c[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, C[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    uint32_t live = 0;
+    if (i < n) {
+        float4 a = lo[i], b = hi[i];
+        if (a.x <= b.x) {
+            live = 1;
+            c[0] = C[0] = 0.5f * (a.x + b.x);
+            c[1] = C[1] = 0.5f * (a.y + b.y);
+            c[2] = C[2] = 0.5f * (a.z + b.z);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+#pragma unroll
+        for (int o = 16; o; o >>= 1) {
+            c[k] = fminf(c[k], __shfl_xor_sync(0xFFFFFFFFu, c[k], o));
+            C[k] = fmaxf(C[k], __shfl_xor_sync(0xFFFFFFFFu, C[k], o));
+        }
+    }
+    const uint32_t nlive = __popc(__ballot_sync(0xFFFFFFFFu, live));
+    if ((threadIdx.x & 31u) == 0 && nlive) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            atomicMin(&bounds[k], enc_f(c[k]));
+            atomicMax(&bounds[3 + k], enc_f(C[k]));
+        }
+        atomicAdd(&bounds[6], nlive);
+    }
+}
+
+__device__ __forceinline__ uint64_t expand21(uint64_t x) {
+    x &= 0x1fffffull;
+    x = (x | x << 32) & 0x1f00000000ffffull;
+    x = (x | x << 16) & 0x1f0000ff0000ffull;
+    x = (x | x << 8) & 0x100f00f00f00f00full;
+    x = (x | x << 4) & 0x10c30c30c30c30c3ull;
+    x = (x | x << 2) & 0x1249249249249249ull;
+    return x;
+}
+
+__global__ void morton_kernel(const float4* __restrict__ lo, const float4* __restrict__ hi, uint32_t n, const uint32_t* __restrict__ bounds,
+                              uint64_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 a = lo[i], b = hi[i];
+    uint64_t key = 0xFFFFFFFFFFFFFFFFull;  // dead boxes sort last
+    if (a.x <= b.x) {
+        const float c[3] = {0.5f * (a.x + b.x), 0.5f * (a.y + b.y), 0.5f * (a.z + b.z)};
+        uint64_t q[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const float mn = dec_f(bounds[k]), mx = dec_f(bounds[3 + k]);
+            const float ext = fmaxf(mx - mn, 1e-30f);
+            float u = (c[k] - mn) / ext;
+            u = fminf(fmaxf(u, 0.0f), 1.0f);
+            q[k] = (uint64_t)min(2097151u, (uint32_t)(u * 2097152.0f));
+        }
+        key = (expand21(q[0]) << 2) | (expand21(q[1]) << 1) | expand21(q[2]);
+    }
+    keys[i] = key;
+    vals[i] = i;
+}
+
+// ------------------------------------------------------------------------------------------- Karras hierarchy
+// Unified node ids: internal i in [0, n-1), leaf j as (n-1)+j.
+__device__ __forceinline__ int delta_fn(const uint64_t* __restrict__ keys, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    const uint64_t a = keys[i], b = keys[j];
+    if (a == b) return 64 + __clz((uint32_t)i ^ (uint32_t)j);
+    return __clzll((long long)(a ^ b));
+}
+
+__global__ void karras_kernel(const uint64_t* __restrict__ keys, int n, uint32_t* __restrict__ left, uint32_t* __restrict__ right,
+                              uint32_t* __restrict__ parent, uint32_t* __restrict__ first, uint32_t* __restrict__ last) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    const int d = (delta_fn(keys, n, i, i + 1) - delta_fn(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    const int dmin = delta_fn(keys, n, i, i - d);
+    int lmax = 2;
+    while (delta_fn(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t >= 1; t >>= 1)
+        if (delta_fn(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    const int j = i + l * d;
+    const int dnode = delta_fn(keys, n, i, j);
+    int s = 0;
+    int t = l;
+    do {
+        t = (t + 1) >> 1;
+        if (delta_fn(keys, n, i, i + (s + t) * d) > dnode) s += t;
+    } while (t > 1);
+    const int gamma = i + s * d + min(d, 0);
+    const int lo = min(i, j), hi = max(i, j);
+    const uint32_t l_id = (lo == gamma) ? (uint32_t)(n - 1 + gamma) : (uint32_t)gamma;
+    const uint32_t r_id = (hi == gamma + 1) ? (uint32_t)(n - 1 + gamma + 1) : (uint32_t)(gamma + 1);
+    left[i] = l_id;
+    right[i] = r_id;
+    parent[l_id] = (uint32_t)i;
+    parent[r_id] = (uint32_t)i;
+    first[i] = (uint32_t)lo;
+    last[i] = (uint32_t)hi;
+    if (i == 0) parent[0] = 0xFFFFFFFFu;
+}
+
+__global__ void leaf_boxes_kernel(const float4* __restrict__ lo, const float4* __restrict__ hi, const uint32_t* __restrict__ perm, uint32_t n,
+                                  float4* __restrict__ blo, float4* __restrict__ bhi) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const uint32_t i = perm[j];
+    blo[n - 1 + j] = lo[i];
+    bhi[n - 1 + j] = hi[i];
+}
+
+__global__ void refit_kernel(uint32_t n, const uint32_t* __restrict__ parent, const uint32_t* __restrict__ left, const uint32_t* __restrict__ right,
+                             float4* blo, float4* bhi, uint32_t* flags) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    uint32_t p = parent[n - 1 + j];
+    while (p != 0xFFFFFFFFu) {
+        __threadfence();
+        if (atomicAdd(&flags[p], 1u) == 0u) return;  // first child to arrive: the sibling will finish the job
+        __threadfence();
+        const uint32_t l = left[p], r = right[p];
+        const float4 la = __ldcg(&blo[l]), lb = __ldcg(&bhi[l]), ra = __ldcg(&blo[r]), rb = __ldcg(&bhi[r]);
+        __stcg(&blo[p], make_float4(fminf(la.x, ra.x), fminf(la.y, ra.y), fminf(la.z, ra.z), 0.f));
+        __stcg(&bhi[p], make_float4(fmaxf(lb.x, rb.x), fmaxf(lb.y, rb.y), fmaxf(lb.z, rb.z), 0.f));
+        p = parent[p];
+    }
+}
+
+// ------------------------------------------------------------------------------------------- collapse to 8-wide
+struct BinTree {
+    const uint32_t *left, *right, *first, *last;
+    const float4 *blo, *bhi;
+    uint32_t n;
+    __device__ __forceinline__ uint32_t count(uint32_t id) const { return id >= n - 1 ? 1u : last[id] - first[id] + 1u; }
+    __device__ __forceinline__ uint32_t start(uint32_t id) const { return id >= n - 1 ? id - (n - 1) : first[id]; }
+};
+
+__device__ __forceinline__ void write_child(WideNode* nd, int k, float4 lo, float4 hi, uint32_t ref) {
+    nd->lox[k] = lo.x; nd->loy[k] = lo.y; nd->loz[k] = lo.z;
+    nd->hix[k] = hi.x; nd->hiy[k] = hi.y; nd->hiz[k] = hi.z;
+    nd->child[k] = ref;
+    nd->pad[k] = 0;
+}
+
+__global__ void collapse_kernel(BinTree T, const uint2* __restrict__ q_in, uint32_t n_in, uint2* __restrict__ q_out, uint32_t* __restrict__ n_out,
+                                uint32_t* __restrict__ node_counter, WideNode* __restrict__ nodes) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_in) return;
+    const uint32_t b = q_in[t].x, w = q_in[t].y;
+    uint32_t slots[WIDE];
+    int ns = 2;
+    slots[0] = T.left[b];
+    slots[1] = T.right[b];
+    while (ns < WIDE) {
+        int best = -1;
+        float bestA = -1.0f;
+        for (int k = 0; k < ns; ++k) {
+            const uint32_t id = slots[k];
+            if (id < T.n - 1 && T.count(id) > (uint32_t)LEAF_MAX) {
+                const float4 a = T.blo[id], c = T.bhi[id];
+                const float ex = c.x - a.x, ey = c.y - a.y, ez = c.z - a.z;
+                const float area = ex * ey + ey * ez + ez * ex;
+                if (area > bestA) { bestA = area; best = k; }
+            }
+        }
+        if (best < 0) break;
+        const uint32_t id = slots[best];
+        slots[best] = T.left[id];
+        slots[ns++] = T.right[id];
+    }
+    WideNode* nd = &nodes[w];
+    for (int k = 0; k < WIDE; ++k) {
+        if (k < ns) {
+            const uint32_t id = slots[k];
+            const uint32_t c = T.count(id);
+            uint32_t ref;
+            if (c <= (uint32_t)LEAF_MAX) {
+                ref = CHILD_LEAF | ((c - 1u) << 28) | T.start(id);
+            } else {
+                const uint32_t wi = atomicAdd(node_counter, 1u);
+                const uint32_t o = atomicAdd(n_out, 1u);
+                q_out[o] = make_uint2(id, wi);
+                ref = wi;
+            }
+            write_child(nd, k, T.blo[id], T.bhi[id], ref);
+        } else {
+            write_child(nd, k, make_float4(INFINITY, INFINITY, INFINITY, 0.f), make_float4(-INFINITY, -INFINITY, -INFINITY, 0.f), CHILD_EMPTY);
+        }
+    }
+}
+
+// n_live <= LEAF_MAX: one node, one leaf child holding everything
+__global__ void tiny_root_kernel(const float4* __restrict__ lo, const float4* __restrict__ hi, const uint32_t* __restrict__ perm, uint32_t n,
+                                 WideNode* __restrict__ nodes) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    float4 a = make_float4(INFINITY, INFINITY, INFINITY, 0.f), b = make_float4(-INFINITY, -INFINITY, -INFINITY, 0.f);
+    for (uint32_t j = 0; j < n; ++j) {
+        const float4 l = lo[perm[j]], h = hi[perm[j]];
+        a.x = fminf(a.x, l.x); a.y = fminf(a.y, l.y); a.z = fminf(a.z, l.z);
+        b.x = fmaxf(b.x, h.x); b.y = fmaxf(b.y, h.y); b.z = fmaxf(b.z, h.z);
+    }
+    write_child(&nodes[0], 0, a, b, CHILD_LEAF | ((n - 1u) << 28) | 0u);
+    for (int k = 1; k < WIDE; ++k)
+        write_child(&nodes[0], k, make_float4(INFINITY, INFINITY, INFINITY, 0.f), make_float4(-INFINITY, -INFINITY, -INFINITY, 0.f), CHILD_EMPTY);
+}
+
+struct DevBuf {  // frees on scope exit
+    void* p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    cudaError_t alloc(size_t bytes) { return cudaMalloc(&p, bytes ? bytes : 1); }
+    template <class T> T* as() { return reinterpret_cast<T*>(p); }
+};
+
+int lbvh_build(const float4* d_lo, const float4* d_hi, uint32_t n, cudaStream_t stream, LbvhResult* out, unsigned long long* launches) {
+    *out = LbvhResult();
+    if (n == 0) return 0;
+    if (n >= (1u << 28)) return (int)cudaErrorInvalidValue;
+    const int TB = 256;
+    DevBuf bounds, keys, keys2, vals2;
+    CK(bounds.alloc(8 * sizeof(uint32_t)));
+    const uint32_t h_init[8] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u, 0u, 0u, 0u};
+    CK(cudaMemcpyAsync(bounds.p, h_init, sizeof(h_init), cudaMemcpyHostToDevice, stream));
+    bounds_kernel<<<cdiv(n, TB), TB, 0, stream>>>(d_lo, d_hi, n, bounds.as<uint32_t>());
+    ++*launches;
+    CK(keys.alloc(sizeof(uint64_t) * n));
+    CK(keys2.alloc(sizeof(uint64_t) * n));
+    CK(vals2.alloc(sizeof(uint32_t) * n));
+    uint32_t* d_perm = nullptr;
+    CK(cudaMalloc(&d_perm, sizeof(uint32_t) * n));
+    out->perm = d_perm;
+    morton_kernel<<<cdiv(n, TB), TB, 0, stream>>>(d_lo, d_hi, n, bounds.as<uint32_t>(), keys.as<uint64_t>(), d_perm);
+    ++*launches;
+    bool in_tmp = false;
+    int rc = radix_sort_pairs(keys.as<uint64_t>(), keys2.as<uint64_t>(), d_perm, vals2.as<uint32_t>(), n, stream, launches, &in_tmp);
+    if (rc) return rc;
+    uint32_t h_bounds[8];
+    CK(cudaMemcpyAsync(h_bounds, bounds.p, sizeof(h_bounds), cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    const uint32_t nl = h_bounds[6];
+    out->n_live = nl;
+    for (int k = 0; k < 3; ++k) { out->lo[k] = dec_f(h_bounds[k]); out->hi[k] = dec_f(h_bounds[3 + k]); }
+    if (nl == 0) return 0;
+
+    if (nl <= (uint32_t)LEAF_MAX) {
+        WideNode* nodes = nullptr;
+        CK(cudaMalloc(&nodes, sizeof(WideNode)));
+        tiny_root_kernel<<<1, 32, 0, stream>>>(d_lo, d_hi, d_perm, nl, nodes);
+        ++*launches;
+        CK(cudaStreamSynchronize(stream));
+        out->nodes = nodes;
+        out->n_nodes = 1;
+        out->levels = 1;
+        return 0;
+    }
+
+    DevBuf left, right, parent, first, last, blo, bhi, flags, qa, qb, ctr, wide_tmp;
+    CK(left.alloc(4ull * (nl - 1)));
+    CK(right.alloc(4ull * (nl - 1)));
+    CK(first.alloc(4ull * (nl - 1)));
+    CK(last.alloc(4ull * (nl - 1)));
+    CK(parent.alloc(4ull * (2ull * nl - 1)));
+    CK(blo.alloc(16ull * (2ull * nl - 1)));
+    CK(bhi.alloc(16ull * (2ull * nl - 1)));
+    CK(flags.alloc(4ull * (nl - 1)));
+    CK(cudaMemsetAsync(flags.p, 0, 4ull * (nl - 1), stream));
+    karras_kernel<<<cdiv(nl - 1, TB), TB, 0, stream>>>(keys.as<uint64_t>(), (int)nl, left.as<uint32_t>(), right.as<uint32_t>(),
+                                                      parent.as<uint32_t>(), first.as<uint32_t>(), last.as<uint32_t>());
+    leaf_boxes_kernel<<<cdiv(nl, TB), TB, 0, stream>>>(d_lo, d_hi, d_perm, nl, blo.as<float4>(), bhi.as<float4>());
+    refit_kernel<<<cdiv(nl, TB), TB, 0, stream>>>(nl, parent.as<uint32_t>(), left.as<uint32_t>(), right.as<uint32_t>(), blo.as<float4>(),
+                                                 bhi.as<float4>(), flags.as<uint32_t>());
+    *launches += 3;
+
+    // collapse, level by level.  Upper bound on wide nodes: every wide node but the root is a binary
+    // internal node with > LEAF_MAX prims, and two such nodes never share a leaf run, so <= nl.
+    const uint32_t max_nodes = nl;
+    CK(wide_tmp.alloc(sizeof(WideNode) * (size_t)max_nodes));
+    CK(qa.alloc(sizeof(uint2) * (size_t)max_nodes));
+    CK(qb.alloc(sizeof(uint2) * (size_t)max_nodes));
+    CK(ctr.alloc(2 * sizeof(uint32_t)));  // [0] = node counter, [1] = n_out
+    const uint2 root_item = make_uint2(0u, 0u);
+    CK(cudaMemcpyAsync(qa.p, &root_item, sizeof(uint2), cudaMemcpyHostToDevice, stream));
+    uint32_t h_ctr[2] = {1u, 0u};
+    CK(cudaMemcpyAsync(ctr.p, h_ctr, sizeof(h_ctr), cudaMemcpyHostToDevice, stream));
+    BinTree T{left.as<uint32_t>(), right.as<uint32_t>(), first.as<uint32_t>(), last.as<uint32_t>(), blo.as<float4>(), bhi.as<float4>(), nl};
+    uint32_t n_in = 1, levels = 0;
+    uint2* qi = qa.as<uint2>();
+    uint2* qo = qb.as<uint2>();
+    while (n_in) {
+        collapse_kernel<<<cdiv(n_in, 128), 128, 0, stream>>>(T, qi, n_in, qo, ctr.as<uint32_t>() + 1, ctr.as<uint32_t>(), wide_tmp.as<WideNode>());
+        ++*launches;
+        ++levels;
+        CK(cudaMemcpyAsync(h_ctr, ctr.p, sizeof(h_ctr), cudaMemcpyDeviceToHost, stream));
+        CK(cudaStreamSynchronize(stream));
+        n_in = h_ctr[1];
+        const uint32_t zero = 0;
+        CK(cudaMemcpyAsync(ctr.as<uint32_t>() + 1, &zero, 4, cudaMemcpyHostToDevice, stream));
+        std::swap(qi, qo);
+        if (levels > 4096) return (int)cudaErrorUnknown;
+    }
+    CK(cudaGetLastError());
+    const uint32_t n_nodes = h_ctr[0];
+    WideNode* nodes = nullptr;
+    CK(cudaMalloc(&nodes, sizeof(WideNode) * (size_t)n_nodes));
+    CK(cudaMemcpyAsync(nodes, wide_tmp.p, sizeof(WideNode) * (size_t)n_nodes, cudaMemcpyDeviceToDevice, stream));
+    CK(cudaStreamSynchronize(stream));
+    out->nodes = nodes;
+    out->n_nodes = n_nodes;
+    out->levels = levels;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------- particles
+// Raw record = reference GaussianParticle, 59 floats: pos[0..2] scale[3..5] rot x,y,z,w [6..9] opacity[10] sh[11..58]
+constexpr int RAW_FLOATS = 59;
+
+struct M3 { float c[3][3]; };  // c[col][row], glm storage
+
+// glm::mat3_cast (third_party/glm/gtc/quaternion.inl:47-72), un-fused IEEE ops in the source order so that
+// host (oracle) and device produce bit-identical matrices.
+__device__ __forceinline__ M3 mat3_cast_rn(float x, float y, float z, float w) {
+    const float qxx = __fmul_rn(x, x), qyy = __fmul_rn(y, y), qzz = __fmul_rn(z, z);
+    const float qxz = __fmul_rn(x, z), qxy = __fmul_rn(x, y), qyz = __fmul_rn(y, z);
+    const float qwx = __fmul_rn(w, x), qwy = __fmul_rn(w, y), qwz = __fmul_rn(w, z);
+    M3 R;
+    R.c[0][0] = __fsub_rn(1.0f, __fmul_rn(2.0f, __fadd_rn(qyy, qzz)));
+    R.c[0][1] = __fmul_rn(2.0f, __fadd_rn(qxy, qwz));
+    R.c[0][2] = __fmul_rn(2.0f, __fsub_rn(qxz, qwy));
+    R.c[1][0] = __fmul_rn(2.0f, __fsub_rn(qxy, qwz));
+    R.c[1][1] = __fsub_rn(1.0f, __fmul_rn(2.0f, __fadd_rn(qxx, qzz)));
+    R.c[1][2] = __fmul_rn(2.0f, __fadd_rn(qyz, qwx));
+    R.c[2][0] = __fmul_rn(2.0f, __fadd_rn(qxz, qwy));
+    R.c[2][1] = __fmul_rn(2.0f, __fsub_rn(qyz, qwx));
+    R.c[2][2] = __fsub_rn(1.0f, __fmul_rn(2.0f, __fadd_rn(qxx, qyy)));
+    return R;
+}
+
+// icosahedron of src/geometry/Icosahedron.h:13-29 (unit in-sphere)
+__constant__ float c_ico[12][3] = {
+    {-0.66158453f, 1.0704663f, 0.f}, {0.66158453f, 1.0704663f, 0.f}, {-0.66158453f, -1.0704663f, 0.f}, {0.66158453f, -1.0704663f, 0.f},
+    {0.f, -0.66158453f, 1.0704663f}, {0.f, 0.66158453f, 1.0704663f}, {0.f, -0.66158453f, -1.0704663f}, {0.f, 0.66158453f, -1.0704663f},
+    {1.0704663f, 0.f, -0.66158453f}, {1.0704663f, 0.f, 0.66158453f}, {-1.0704663f, 0.f, -0.66158453f}, {-1.0704663f, 0.f, 0.66158453f}};
+
+__global__ void particle_boxes_kernel(const float* __restrict__ raw, const float* __restrict__ s_arr, uint32_t n, float4* __restrict__ lo,
+                                      float4* __restrict__ hi) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float* p = raw + (size_t)i * RAW_FLOATS;
+    const float s = s_arr[i];
+    float4 a = make_float4(1.f, 1.f, 1.f, 0.f), b = make_float4(-1.f, -1.f, -1.f, 0.f);  // dead: lo > hi
+    if (s > 0.0f) {
+        const M3 R = mat3_cast_rn(p[6], p[7], p[8], p[9]);
+        const float sx = p[3] * s, sy = p[4] * s, sz = p[5] * s;
+        float mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+        for (int v = 0; v < 12; ++v) {
+            const float vx = sx * c_ico[v][0], vy = sy * c_ico[v][1], vz = sz * c_ico[v][2];
+#pragma unroll
+            for (int r = 0; r < 3; ++r) {
+                const float wv = p[r] + (R.c[0][r] * vx + R.c[1][r] * vy + R.c[2][r] * vz);
+                mn[r] = fminf(mn[r], wv);
+                mx[r] = fmaxf(mx[r], wv);
+            }
+        }
+        bool ok = true;
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+            // conservative padding: the slab test of the trace kernel runs in Gaussian space, so the world-space
+            // box must absorb both roundings.  1e-4 of the extent is ~3 orders above fp32 noise.
+            const float pad = 1e-4f * (mx[r] - mn[r]) + 1e-5f * fmaxf(fabsf(mn[r]), fabsf(mx[r])) + 1e-7f;
+            mn[r] -= pad;
+            mx[r] += pad;
+            ok = ok && isfinite(mn[r]) && isfinite(mx[r]);
+        }
+        if (ok) {
+            a = make_float4(mn[0], mn[1], mn[2], 0.f);
+            b = make_float4(mx[0], mx[1], mx[2], 0.f);
+        }
+    }
+    lo[i] = a;
+    hi[i] = b;
+}
+
+__global__ void particle_gather_kernel(const float* __restrict__ raw, const float* __restrict__ s_arr, const uint32_t* __restrict__ perm,
+                                       uint32_t n_live, PRec* __restrict__ recs, float4* __restrict__ sh) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n_live) return;
+    const uint32_t i = perm[j];
+    const float* p = raw + (size_t)i * RAW_FLOATS;
+    const M3 R = mat3_cast_rn(p[6], p[7], p[8], p[9]);
+    float A[3][3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+        const float inv = __fdiv_rn(1.0f, p[3 + r]);  // inv_s[r][r] = 1.0f / gp.scale (tracer.cuh:196-199)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) A[r][c] = __fmul_rn(inv, R.c[r][c]);  // (inv_s * RT): row r of A = column r of R, scaled
+    }
+    PRec rec;
+    rec.q0 = make_float4(A[0][0], A[0][1], A[0][2], A[1][0]);
+    rec.q1 = make_float4(A[1][1], A[1][2], A[2][0], A[2][1]);
+    rec.q2 = make_float4(A[2][2], p[0], p[1], p[2]);
+    rec.q3 = make_float4(s_arr[i], p[10], __uint_as_float(i), 0.f);
+    recs[j] = rec;
+    float4* o = sh + (size_t)j * SH_F4;
+#pragma unroll
+    for (int k = 0; k < SH_F4; ++k) o[k] = make_float4(p[11 + 4 * k], p[12 + 4 * k], p[13 + 4 * k], p[14 + 4 * k]);
+}
+
+int particles_compute_boxes(const void* d_particles236, const float* d_s, uint32_t n, float4* d_lo, float4* d_hi, cudaStream_t stream,
+                            unsigned long long* launches) {
+    if (!n) return 0;
+    particle_boxes_kernel<<<cdiv(n, 128), 128, 0, stream>>>((const float*)d_particles236, d_s, n, d_lo, d_hi);
+    ++*launches;
+    return (int)cudaGetLastError();
+}
+
+int particles_gather(const void* d_particles236, const float* d_s, const uint32_t* d_perm, uint32_t n_live, PRec* d_recs, float4* d_sh,
+                     cudaStream_t stream, unsigned long long* launches) {
+    if (!n_live) return 0;
+    particle_gather_kernel<<<cdiv(n_live, 128), 128, 0, stream>>>((const float*)d_particles236, d_s, d_perm, n_live, d_recs, d_sh);
+    ++*launches;
+    return (int)cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------- meshes
+__global__ void tri_boxes_kernel(const float* __restrict__ tri9, uint32_t n, float4* __restrict__ lo, float4* __restrict__ hi) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float* t = tri9 + (size_t)i * 9;
+    float mn[3], mx[3];
+    bool ok = true;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        mn[k] = fminf(t[k], fminf(t[3 + k], t[6 + k]));
+        mx[k] = fmaxf(t[k], fmaxf(t[3 + k], t[6 + k]));
+        const float pad = 1e-4f * (mx[k] - mn[k]) + 1e-5f * fmaxf(fabsf(mn[k]), fabsf(mx[k])) + 1e-7f;
+        mn[k] -= pad;
+        mx[k] += pad;
+        ok = ok && isfinite(mn[k]) && isfinite(mx[k]);
+    }
+    lo[i] = ok ? make_float4(mn[0], mn[1], mn[2], 0.f) : make_float4(1.f, 1.f, 1.f, 0.f);
+    hi[i] = ok ? make_float4(mx[0], mx[1], mx[2], 0.f) : make_float4(-1.f, -1.f, -1.f, 0.f);
+}
+
+__global__ void tri_gather_kernel(const float* __restrict__ tri9, const uint2* __restrict__ meta, const uint32_t* __restrict__ perm, uint32_t n,
+                                  TriRec* __restrict__ out) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const uint32_t i = perm[j];
+    const float* t = tri9 + (size_t)i * 9;
+    const uint2 m = meta[i];
+    TriRec r;
+    r.a = make_float4(t[0], t[1], t[2], __uint_as_float(m.x));
+    r.b = make_float4(__fsub_rn(t[3], t[0]), __fsub_rn(t[4], t[1]), __fsub_rn(t[5], t[2]), __uint_as_float(m.y));
+    r.c = make_float4(__fsub_rn(t[6], t[0]), __fsub_rn(t[7], t[1]), __fsub_rn(t[8], t[2]), 0.f);
+    out[j] = r;
+}
+
+int mesh_compute_boxes(const float* d_tri9, uint32_t n, float4* d_lo, float4* d_hi, cudaStream_t stream, unsigned long long* launches) {
+    if (!n) return 0;
+    tri_boxes_kernel<<<cdiv(n, 128), 128, 0, stream>>>(d_tri9, n, d_lo, d_hi);
+    ++*launches;
+    return (int)cudaGetLastError();
+}
+int mesh_gather(const float* d_tri9, const uint2* d_meta, const uint32_t* d_perm, uint32_t n, TriRec* out, cudaStream_t stream,
+                unsigned long long* launches) {
+    if (!n) return 0;
+    tri_gather_kernel<<<cdiv(n, 128), 128, 0, stream>>>(d_tri9, d_meta, d_perm, n, out);
+    ++*launches;
+    return (int)cudaGetLastError();
+}
+
+}  // namespace grt

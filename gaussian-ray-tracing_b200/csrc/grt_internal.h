@@ -1,0 +1,114 @@
+// grt_internal.h -- device data layout shared by the build and trace translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/grt.h"
+
+namespace grt {
+
+constexpr int WIDE = 8;            // children per wide node
+constexpr int LEAF_MAX = 4;        // proxies (or triangles) per leaf child
+constexpr uint32_t CHILD_EMPTY = 0xFFFFFFFFu;
+constexpr uint32_t CHILD_LEAF = 0x80000000u;  // leaf: CHILD_LEAF | (count-1) << 28 | start (28 bits)
+constexpr uint32_t INVALID_ID = 0xFFFFFFFFu;
+
+// Packed per-particle geometry record, 64 B, in Morton (BVH leaf) order.  Four 128-bit loads.
+//   q0 = A00 A01 A02 A10   q1 = A11 A12 A20 A21   q2 = A22 mu.x mu.y mu.z   q3 = s opacity id(bits) 0
+// A = diag(1/scale) * R^T  (shaders/tracer.cuh:194-201), s = proxy in-sphere radius in Gaussian space
+// (src/GaussianTracer.cpp:306).
+struct __align__(16) PRec {
+    float4 q0, q1, q2, q3;
+};
+static_assert(sizeof(PRec) == 64, "PRec");
+
+// SH coefficients in the same order: 16 x float3 = 12 float4 per particle (shaders/tracer.cuh:218-221).
+constexpr int SH_F4 = 12;
+
+// 8-wide BVH node, SoA so that one warp-uniform 128-bit load fetches 4 children's plane.
+struct __align__(16) WideNode {
+    float lox[WIDE], loy[WIDE], loz[WIDE], hix[WIDE], hiy[WIDE], hiz[WIDE];
+    uint32_t child[WIDE];
+    uint32_t pad[WIDE];
+};
+static_assert(sizeof(WideNode) == 256, "WideNode");
+
+// Triangle record for the reflection primitives, 48 B: v0|mesh, e1|face, e2|0  (e = v1-v0, v2-v0)
+struct __align__(16) TriRec {
+    float4 a, b, c;
+};
+
+// What Params.handle / Params.mesh_handle point at (device memory; the value is validated against the
+// context's own handles on the host before launch).
+struct AccelHeader {
+    uint64_t magic;
+    const WideNode* nodes;
+    const PRec* recs;     // particles
+    const float4* sh;     // particles
+    const TriRec* tris;   // meshes
+    uint32_t n_prims;
+    uint32_t n_nodes;
+};
+constexpr uint64_t ACCEL_MAGIC_PARTICLES = 0x4752545041525431ull;  // "GRTPART1"
+constexpr uint64_t ACCEL_MAGIC_MESH = 0x4752544d45534831ull;       // "GRTMESH1"
+
+// reference's Mesh (src/Parameters.h:36-40)
+struct MeshDev {
+    uint3* faces;
+    float3* vertex_normals;
+};
+
+struct DeviceCounters {
+    unsigned long long rays, segments, rounds, hits_gathered, hits_shaded, warp_nodes, warp_leaf_prims, warp_rounds,
+        stack_overflow;
+};
+
+// Extra kernel arguments next to the 144-byte Params.
+struct LaunchExtras {
+    const WideNode* p_nodes;
+    const PRec* p_recs;
+    const float4* p_sh;
+    uint32_t p_count;
+    const WideNode* m_nodes;
+    const TriRec* m_tris;
+    uint32_t m_count;
+    uint32_t x0, y0, w, h;  // pixel rectangle
+    float* rgb32f;
+    uint32_t* trace_ids;
+    uint32_t* trace_counts;
+    uint32_t tx0, ty0, tw, th, trace_max;
+    DeviceCounters* counters;
+};
+
+// ---- generic LBVH builder (build.cu) ----
+struct BuildScratch;
+struct LbvhResult {
+    WideNode* nodes = nullptr;  // cudaMalloc'd, exact size
+    uint32_t n_nodes = 0;
+    uint32_t* perm = nullptr;   // sorted position -> input index, n_live entries valid (cudaMalloc'd, n entries)
+    uint32_t n_live = 0;
+    uint32_t levels = 0;
+    float lo[3], hi[3];
+};
+// d_lo/d_hi: n boxes (float4, w ignored); dead boxes must have lo.x > hi.x (they sort last and are dropped).
+// Returns cudaError_t as int; launches counted into *launches.
+int lbvh_build(const float4* d_lo, const float4* d_hi, uint32_t n, cudaStream_t stream, LbvhResult* out,
+               unsigned long long* launches);
+int radix_sort_pairs(uint64_t* d_keys, uint64_t* d_keys_tmp, uint32_t* d_vals, uint32_t* d_vals_tmp, uint32_t n,
+                     cudaStream_t stream, unsigned long long* launches, bool* result_in_tmp);
+
+// particle pack kernels (build.cu)
+int particles_compute_boxes(const void* d_particles236, const float* d_s, uint32_t n, float4* d_lo, float4* d_hi,
+                            cudaStream_t stream, unsigned long long* launches);
+int particles_gather(const void* d_particles236, const float* d_s, const uint32_t* d_perm, uint32_t n_live, PRec* d_recs,
+                     float4* d_sh, cudaStream_t stream, unsigned long long* launches);
+// triangle soup: d_tri9 = n x 9 floats (world-space v0,v1,v2), d_meta = n x (mesh, face)
+int mesh_compute_boxes(const float* d_tri9, uint32_t n_tris, float4* d_lo, float4* d_hi, cudaStream_t stream,
+                       unsigned long long* launches);
+int mesh_gather(const float* d_tri9, const uint2* d_meta, const uint32_t* d_perm, uint32_t n, TriRec* out,
+                cudaStream_t stream, unsigned long long* launches);
+
+// trace kernel (trace.cu)
+int launch_trace(const grtParams& p, const LaunchExtras& ex, bool counters, cudaStream_t stream);
+
+}  // namespace grt

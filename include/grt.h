@@ -1,0 +1,155 @@
+/*
+ * grt.h -- C ABI of libgrt.so, the B200 (sm_100a) software Gaussian ray tracer.
+ *
+ * This is the drop-in boundary for the one hot path of Ray-Studio2/gaussian-ray-tracing: everything the
+ * reference host does through OptiX for that path.  Each entry point names the reference call it replaces
+ * (file:line relative to the reference repository).  Plain pointers and sizes only; no C++/torch types.
+ *
+ * Conventions: every function returns 0 on success, non-zero on failure (grtGetLastError() gives the
+ * text; the C++ facade turns it into std::runtime_error like the reference's CUDA_CHECK/OPTIX_CHECK,
+ * src/Exception.h:31-80).  `stream` arguments are cudaStream_t passed as void* (NULL = default stream).
+ * A context is bound to one GPU and is not thread-safe.  There is NO CPU fallback: without a CUDA
+ * device grtCreate fails.
+ */
+#ifndef GRT_H
+#define GRT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GRT_VERSION 100
+
+/* Byte-identical to the reference's `struct Params` (src/Parameters.h:42-74): 144 bytes, offsets
+ * out@0 width@8 height@12 sh_degree_max@16 eye@20 U@32 V@44 W@56 t_min@68 t_max@72 minTransmittance@76
+ * alpha_min@80 handle@88 d_particles@96 mesh_handle@104 mode_fisheye@112 d_meshes@120 type@128 traceState@136. */
+typedef struct grtParams {
+    void* output_buffer;      /* device uchar3*, width*height, index y*width+x */
+    uint32_t width;
+    uint32_t height;
+    uint32_t sh_degree_max;   /* 0..3 */
+    float eye[3];
+    float U[3];
+    float V[3];
+    float W[3];
+    float t_min;
+    float t_max;
+    float minTransmittance;
+    float alpha_min;
+    uint64_t handle;          /* opaque: from grtBuildParticleAccel (replaces OptixTraversableHandle) */
+    void* d_particles;        /* device copy of the 236-byte GaussianParticle records */
+    uint64_t mesh_handle;     /* opaque: from grtBuildMeshAccel; 0 = no reflection primitives */
+    uint8_t mode_fisheye;     /* C++ bool */
+    void* d_meshes;           /* device Mesh{uint3* faces; float3* vertex_normals}[] (src/Parameters.h:36-40) */
+    int32_t type;             /* MeshType: 0 MIRROR, 1 NORMAL, 2 GLASS */
+    uint32_t* traceState;     /* kept for layout compatibility; unused (state lives in registers) */
+} grtParams;
+
+/* One reflection primitive as the reference's `Primitive` holds it (src/geometry/Primitives.h:14-29):
+ * object-space vertices/normals, triangle indices and a glm column-major 4x4 transform. */
+typedef struct grtMeshDesc {
+    const float* vertices;    /* vertex_count x 3 */
+    const float* normals;     /* vertex_count x 3 */
+    const uint32_t* indices;  /* index_count (3 per triangle) */
+    uint32_t vertex_count;
+    uint32_t index_count;
+    float transform[16];      /* column-major (glm::mat4) */
+} grtMeshDesc;
+
+typedef struct grtBuildInfo {
+    uint64_t n_particles;     /* records uploaded */
+    uint64_t n_live;          /* opacity > alpha_min (the rest can never be hit: SURVEY app. A item 4) */
+    uint32_t n_wide_nodes;
+    uint32_t wide_depth_levels;
+    uint32_t n_mesh_triangles;
+    uint32_t n_mesh_wide_nodes;
+    float build_ms;           /* device time of the last particle-accel build */
+    float mesh_build_ms;
+    float scene_lo[3], scene_hi[3];
+} grtBuildInfo;
+
+typedef struct grtCounters {
+    uint64_t rays;
+    uint64_t segments;        /* traceGaussians-equivalents */
+    uint64_t rounds;          /* k-buffer gathers (optixTrace-equivalents), per ray */
+    uint64_t hits_gathered;   /* h_g */
+    uint64_t hits_shaded;     /* h_s */
+    uint64_t warp_nodes;      /* wide nodes expanded, per warp */
+    uint64_t warp_leaf_prims; /* proxy records tested, per warp (x32 lanes of arithmetic) */
+    uint64_t warp_rounds;
+    uint64_t stack_overflow;  /* must stay 0 */
+    uint64_t kernel_launches; /* launches issued by this context since creation (all kernels) */
+} grtCounters;
+
+typedef struct grtContext grtContext;
+
+/* -- lifetime (replaces optixInit/optixDeviceContextCreate + module/pipeline/SBT creation,
+ *    src/GaussianTracer.cpp:72-295: there is nothing to JIT, the kernels are linked in) -- */
+int grtCreate(int device, grtContext** ctx_out);
+int grtDestroy(grtContext* ctx);
+const char* grtGetLastError(const grtContext* ctx); /* ctx may be NULL: error of a failed grtCreate */
+
+/* -- scene (replaces the particle upload of initializeParams, src/GaussianTracer.cpp:491-502) --
+ * host_particles: n records of 236 bytes (GaussianParticle, src/GaussianData.h:12-20).
+ * alpha_min sizes the proxies: s = sqrt(2 ln(opacity/alpha_min)) (src/GaussianTracer.cpp:306). */
+int grtSetParticles(grtContext* ctx, const void* host_particles, uint64_t n, float alpha_min);
+
+/* replaces createGaussianParticlesBVH: createGAS + N x createIAS + optixAccelBuild
+ * (src/GaussianTracer.cpp:297-317, 379, 401-473).  LBVH on the device.  handle_out -> Params.handle,
+ * d_particles_out -> Params.d_particles. */
+int grtBuildParticleAccel(grtContext* ctx, void* stream, uint64_t* handle_out, void** d_particles_out);
+
+/* replaces createGAS/createIAS/buildAccelationStructure for meshes + sendGeometryAttributesToDevice
+ * (src/GaussianTracer.cpp:578-709, 711-794).  n == 0 clears them (removePrimitive, :553-566):
+ * mesh_handle_out = 0, d_meshes_out = NULL. */
+int grtSetMeshes(grtContext* ctx, const grtMeshDesc* meshes, uint32_t n);
+int grtBuildMeshAccel(grtContext* ctx, void* stream, uint64_t* mesh_handle_out, void** d_meshes_out);
+
+/* -- render (replaces cudaMemcpyAsync(d_params) + optixLaunch(w,h,1), src/GaussianTracer.cpp:517-534) --
+ * Asynchronous on `stream`.  host_params is read before returning. */
+int grtLaunch(grtContext* ctx, void* stream, const grtParams* host_params);
+/* Only the pixel rectangle [x0,x0+w) x [y0,y0+h) of the frame is traced (multi-GPU tile partition). */
+int grtLaunchTile(grtContext* ctx, void* stream, const grtParams* host_params, uint32_t x0, uint32_t y0, uint32_t w, uint32_t h);
+/* n cameras, one full frame each (output_buffer per entry). */
+int grtLaunchBatch(grtContext* ctx, void* stream, const grtParams* host_params_array, uint32_t n);
+/* End-to-end convenience with HOST output: traces rows [y0,y0+h) into a context-owned device frame,
+ * copies those rows to host_rgb8 + 3*width*y0 (pinned or pageable) and synchronises.
+ * host_params->output_buffer is ignored. h == 0 means the full frame. */
+int grtRenderHost(grtContext* ctx, const grtParams* host_params, uint8_t* host_rgb8, uint32_t y0, uint32_t h);
+
+/* -- parity / profiling side channels (not in the reference; Params layout untouched) --
+ * d_rgb32f: width*height*3 floats, accumColor before clamp+quantise (NULL disables).
+ * Hit-ID traces for the pixel rectangle (tx0,ty0,tw,th): the first trace_max consumed particle IDs per
+ * pixel go to d_trace_ids[((y-ty0)*tw+(x-tx0))*trace_max + k], the total count to d_trace_counts[...]. */
+int grtSetDebugOutputs(grtContext* ctx, float* d_rgb32f, uint32_t* d_trace_ids, uint32_t* d_trace_counts,
+                       uint32_t tx0, uint32_t ty0, uint32_t tw, uint32_t th, uint32_t trace_max);
+int grtEnableCounters(grtContext* ctx, int enable); /* selects the counting kernel variant */
+int grtGetCounters(grtContext* ctx, grtCounters* out, int reset);
+int grtGetBuildInfo(grtContext* ctx, grtBuildInfo* out);
+/* Walks the built wide BVH on the host: every live record referenced exactly once, every leaf box inside
+ * its ancestors' boxes.  Returns 0 if valid. which: 0 particles, 1 meshes. */
+int grtValidateAccel(grtContext* ctx, int which);
+/* Last kernel's device time (cudaEvent pair recorded around the most recent grtLaunch*), ms. */
+int grtLastLaunchMs(grtContext* ctx, float* ms_out);
+
+/* -- small device-memory helpers so that a C/ctypes caller needs no other CUDA binding -- */
+int grtMalloc(grtContext* ctx, size_t bytes, void** d_ptr_out);
+int grtFree(grtContext* ctx, void* d_ptr);
+int grtMallocHost(grtContext* ctx, size_t bytes, void** h_ptr_out); /* pinned */
+int grtFreeHost(grtContext* ctx, void* h_ptr);
+int grtMemcpyDtoH(grtContext* ctx, void* dst_host, const void* src_dev, size_t bytes, void* stream);
+int grtMemcpyHtoD(grtContext* ctx, void* dst_dev, const void* src_host, size_t bytes, void* stream);
+int grtMemset(grtContext* ctx, void* d_ptr, int value, size_t bytes, void* stream);
+int grtStreamCreate(grtContext* ctx, void** stream_out);
+int grtStreamDestroy(grtContext* ctx, void* stream);
+int grtStreamSynchronize(grtContext* ctx, void* stream);
+/* Sorts n (key,value) pairs with the hand-written device radix sort used by the LBVH build (test hook). */
+int grtDebugRadixSort(grtContext* ctx, uint64_t* host_keys, uint32_t* host_vals, uint64_t n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GRT_H */
