@@ -1,0 +1,552 @@
+// capi.cu -- implementation of the C ABI declared in include/grt.h (the drop-in boundary).
+// Host-side only: owns device memory, validates handles, launches the kernels of build.cu / trace.cu.
+// There is no CPU fallback anywhere in this library.
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "grt_internal.h"
+
+using namespace grt;
+
+static_assert(sizeof(grtParams) == 144, "grtParams must match the reference Params (144 bytes)");
+static_assert(offsetof(grtParams, width) == 8 && offsetof(grtParams, eye) == 20 && offsetof(grtParams, U) == 32 &&
+                  offsetof(grtParams, V) == 44 && offsetof(grtParams, W) == 56 && offsetof(grtParams, t_min) == 68 &&
+                  offsetof(grtParams, alpha_min) == 80 && offsetof(grtParams, handle) == 88 && offsetof(grtParams, d_particles) == 96 &&
+                  offsetof(grtParams, mesh_handle) == 104 && offsetof(grtParams, mode_fisheye) == 112 &&
+                  offsetof(grtParams, d_meshes) == 120 && offsetof(grtParams, type) == 128 && offsetof(grtParams, traceState) == 136,
+              "grtParams offsets must match src/Parameters.h:42-74");
+
+struct grtContext {
+    int device = 0;
+    std::string last_error;
+    unsigned long long launches = 0;
+    // particles
+    uint64_t n_particles = 0;
+    float alpha_min_build = 0.01f;
+    void* d_particles = nullptr;  // 236-byte records
+    float* d_s = nullptr;         // proxy in-sphere radius per particle (0 = culled)
+    WideNode* p_nodes = nullptr;
+    PRec* p_recs = nullptr;
+    float4* p_sh = nullptr;
+    AccelHeader* d_p_header = nullptr;
+    uint32_t p_live = 0, p_nnodes = 0, p_levels = 0;
+    // meshes
+    std::vector<float> h_tri9;
+    std::vector<uint2> h_meta;
+    std::vector<std::vector<float>> h_normals;  // per mesh, transformed
+    std::vector<std::vector<uint32_t>> h_faces; // per mesh
+    std::vector<void*> mesh_allocs;             // per-mesh device arrays
+    MeshDev* d_meshes = nullptr;
+    WideNode* m_nodes = nullptr;
+    TriRec* m_tris = nullptr;
+    AccelHeader* d_m_header = nullptr;
+    uint32_t m_count = 0, m_nnodes = 0;
+    // debug / counters
+    float* dbg_rgb32f = nullptr;
+    uint32_t* dbg_trace_ids = nullptr;
+    uint32_t* dbg_trace_counts = nullptr;
+    uint32_t tx0 = 0, ty0 = 0, tw = 0, th = 0, trace_max = 0;
+    bool counters_on = false;
+    DeviceCounters* d_counters = nullptr;
+    // e2e frame
+    uint8_t* d_frame = nullptr;
+    size_t frame_bytes = 0;
+    cudaStream_t own_stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool ev_valid = false;
+    grtBuildInfo info{};
+};
+
+static std::string g_create_error;
+
+static int fail(grtContext* ctx, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (ctx) ctx->last_error = buf; else g_create_error = buf;
+    return 1;
+}
+#define CU(ctx, call)                                                                              \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) return fail(ctx, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+#define RC(ctx, call)                                                                                            \
+    do {                                                                                                         \
+        int r_ = (call);                                                                                         \
+        if (r_) return fail(ctx, "%s failed: %s (%s:%d)", #call, cudaGetErrorString((cudaError_t)r_), __FILE__, __LINE__); \
+    } while (0)
+
+static void free_particle_accel(grtContext* c) {
+    cudaFree(c->p_nodes); cudaFree(c->p_recs); cudaFree(c->p_sh); cudaFree(c->d_p_header);
+    c->p_nodes = nullptr; c->p_recs = nullptr; c->p_sh = nullptr; c->d_p_header = nullptr;
+    c->p_live = c->p_nnodes = c->p_levels = 0;
+}
+static void free_mesh_accel(grtContext* c) {
+    cudaFree(c->m_nodes); cudaFree(c->m_tris); cudaFree(c->d_m_header); cudaFree(c->d_meshes);
+    for (void* p : c->mesh_allocs) cudaFree(p);
+    c->mesh_allocs.clear();
+    c->m_nodes = nullptr; c->m_tris = nullptr; c->d_m_header = nullptr; c->d_meshes = nullptr;
+    c->m_count = c->m_nnodes = 0;
+}
+
+extern "C" {
+
+int grtCreate(int device, grtContext** ctx_out) {
+    if (!ctx_out) return fail(nullptr, "grtCreate: ctx_out is NULL");
+    *ctx_out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(nullptr, "grtCreate: no CUDA device (%s); libgrt has no CPU fallback", cudaGetErrorString(e));
+    if (device < 0 || device >= count) return fail(nullptr, "grtCreate: device %d out of range (0..%d)", device, count - 1);
+    CU(nullptr, cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CU(nullptr, cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) return fail(nullptr, "grtCreate: device %d is sm_%d%d; libgrt is built for sm_100a only", device, prop.major, prop.minor);
+    grtContext* c = new grtContext();
+    c->device = device;
+    if (cudaMalloc(&c->d_counters, sizeof(DeviceCounters)) != cudaSuccess || cudaMemset(c->d_counters, 0, sizeof(DeviceCounters)) != cudaSuccess ||
+        cudaStreamCreate(&c->own_stream) != cudaSuccess || cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess) {
+        delete c;
+        return fail(nullptr, "grtCreate: device allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
+    }
+    *ctx_out = c;
+    return 0;
+}
+
+int grtDestroy(grtContext* c) {
+    if (!c) return 0;
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    free_particle_accel(c);
+    free_mesh_accel(c);
+    cudaFree(c->d_particles); cudaFree(c->d_s); cudaFree(c->d_counters); cudaFree(c->d_frame);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    delete c;
+    return 0;
+}
+
+const char* grtGetLastError(const grtContext* ctx) { return ctx ? ctx->last_error.c_str() : g_create_error.c_str(); }
+
+// ---------------------------------------------------------------- memory helpers
+int grtMalloc(grtContext* c, size_t bytes, void** out) {
+    if (!c || !out) return fail(c, "grtMalloc: bad argument");
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaMalloc(out, bytes ? bytes : 1));
+    return 0;
+}
+int grtFree(grtContext* c, void* p) { if (!c) return 1; CU(c, cudaFree(p)); return 0; }
+int grtMallocHost(grtContext* c, size_t bytes, void** out) {
+    if (!c || !out) return fail(c, "grtMallocHost: bad argument");
+    CU(c, cudaMallocHost(out, bytes ? bytes : 1));
+    return 0;
+}
+int grtFreeHost(grtContext* c, void* p) { if (!c) return 1; CU(c, cudaFreeHost(p)); return 0; }
+int grtMemcpyDtoH(grtContext* c, void* dst, const void* src, size_t bytes, void* stream) {
+    if (!c) return 1;
+    CU(c, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    CU(c, cudaStreamSynchronize((cudaStream_t)stream));
+    return 0;
+}
+int grtMemcpyHtoD(grtContext* c, void* dst, const void* src, size_t bytes, void* stream) {
+    if (!c) return 1;
+    CU(c, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    CU(c, cudaStreamSynchronize((cudaStream_t)stream));
+    return 0;
+}
+int grtMemset(grtContext* c, void* p, int value, size_t bytes, void* stream) {
+    if (!c) return 1;
+    CU(c, cudaMemsetAsync(p, value, bytes, (cudaStream_t)stream));
+    return 0;
+}
+int grtStreamCreate(grtContext* c, void** out) {
+    if (!c || !out) return 1;
+    cudaStream_t s;
+    CU(c, cudaStreamCreate(&s));
+    *out = (void*)s;
+    return 0;
+}
+int grtStreamDestroy(grtContext* c, void* s) { if (!c) return 1; CU(c, cudaStreamDestroy((cudaStream_t)s)); return 0; }
+int grtStreamSynchronize(grtContext* c, void* s) { if (!c) return 1; CU(c, cudaStreamSynchronize((cudaStream_t)s)); return 0; }
+
+// ---------------------------------------------------------------- particles
+int grtSetParticles(grtContext* c, const void* host_particles, uint64_t n, float alpha_min) {
+    if (!c) return 1;
+    if (n && !host_particles) return fail(c, "grtSetParticles: host_particles is NULL");
+    if (n >= (1ull << 28)) return fail(c, "grtSetParticles: %llu particles exceed the 2^28 limit", (unsigned long long)n);
+    CU(c, cudaSetDevice(c->device));
+    free_particle_accel(c);
+    cudaFree(c->d_particles); cudaFree(c->d_s);
+    c->d_particles = nullptr; c->d_s = nullptr;
+    c->n_particles = n;
+    c->alpha_min_build = alpha_min;
+    if (n == 0) return 0;
+    // Proxy size, exactly as the reference host computes it (src/GaussianTracer.cpp:304-306):
+    //   s = sqrtf(2 ln(opacity / alpha_min)); opacity <= alpha_min gives 0/NaN -> the instance can never be hit
+    //    -> s = 0 marks the particle culled.
+    std::vector<float> s(n);
+    const float* raw = reinterpret_cast<const float*>(host_particles);
+    for (uint64_t i = 0; i < n; ++i) {
+        const float opacity = raw[i * 59 + 10];
+        float v = 0.0f;
+        if (opacity > alpha_min) {
+            v = sqrtf(2.0f * logf(opacity / alpha_min));
+            if (!(v > 0.0f) || !std::isfinite(v)) v = 0.0f;
+        }
+        s[i] = v;
+    }
+    CU(c, cudaMalloc(&c->d_particles, n * 236ull));
+    CU(c, cudaMalloc(&c->d_s, n * sizeof(float)));
+    CU(c, cudaMemcpy(c->d_particles, host_particles, n * 236ull, cudaMemcpyHostToDevice));
+    CU(c, cudaMemcpy(c->d_s, s.data(), n * sizeof(float), cudaMemcpyHostToDevice));
+    return 0;
+}
+
+int grtBuildParticleAccel(grtContext* c, void* stream_v, uint64_t* handle_out, void** d_particles_out) {
+    if (!c) return 1;
+    cudaStream_t stream = (cudaStream_t)stream_v;
+    CU(c, cudaSetDevice(c->device));
+    free_particle_accel(c);
+    if (handle_out) *handle_out = 0;
+    if (d_particles_out) *d_particles_out = c->d_particles;
+    c->info.n_particles = c->n_particles;
+    c->info.n_live = 0; c->info.n_wide_nodes = 0; c->info.wide_depth_levels = 0; c->info.build_ms = 0;
+    if (c->n_particles == 0) return 0;
+    const uint32_t n = (uint32_t)c->n_particles;
+    cudaEvent_t e0, e1;
+    CU(c, cudaEventCreate(&e0));
+    CU(c, cudaEventCreate(&e1));
+    CU(c, cudaEventRecord(e0, stream));
+    float4 *d_lo = nullptr, *d_hi = nullptr;
+    CU(c, cudaMalloc(&d_lo, sizeof(float4) * (size_t)n));
+    CU(c, cudaMalloc(&d_hi, sizeof(float4) * (size_t)n));
+    int rc = particles_compute_boxes(c->d_particles, c->d_s, n, d_lo, d_hi, stream, &c->launches);
+    LbvhResult res;
+    if (!rc) rc = lbvh_build(d_lo, d_hi, n, stream, &res, &c->launches);
+    cudaFree(d_lo); cudaFree(d_hi);
+    if (rc) { cudaFree(res.perm); cudaFree(res.nodes); return fail(c, "particle accel build failed: %s", cudaGetErrorString((cudaError_t)rc)); }
+    c->p_live = res.n_live; c->p_nnodes = res.n_nodes; c->p_levels = res.levels; c->p_nodes = res.nodes;
+    if (res.n_live) {
+        CU(c, cudaMalloc(&c->p_recs, sizeof(PRec) * (size_t)res.n_live));
+        CU(c, cudaMalloc(&c->p_sh, sizeof(float4) * SH_F4 * (size_t)res.n_live));
+        RC(c, particles_gather(c->d_particles, c->d_s, res.perm, res.n_live, c->p_recs, c->p_sh, stream, &c->launches));
+        AccelHeader h{};
+        h.magic = ACCEL_MAGIC_PARTICLES; h.nodes = c->p_nodes; h.recs = c->p_recs; h.sh = c->p_sh; h.tris = nullptr;
+        h.n_prims = res.n_live; h.n_nodes = res.n_nodes;
+        CU(c, cudaMalloc(&c->d_p_header, sizeof(AccelHeader)));
+        CU(c, cudaMemcpyAsync(c->d_p_header, &h, sizeof(h), cudaMemcpyHostToDevice, stream));
+    }
+    CU(c, cudaEventRecord(e1, stream));
+    CU(c, cudaStreamSynchronize(stream));
+    cudaFree(res.perm);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    c->info.n_live = res.n_live; c->info.n_wide_nodes = res.n_nodes; c->info.wide_depth_levels = res.levels; c->info.build_ms = ms;
+    for (int k = 0; k < 3; ++k) { c->info.scene_lo[k] = res.lo[k]; c->info.scene_hi[k] = res.hi[k]; }
+    if (handle_out) *handle_out = (uint64_t)(uintptr_t)c->d_p_header;  // 0 when nothing is live
+    return 0;
+}
+
+// ---------------------------------------------------------------- meshes
+int grtSetMeshes(grtContext* c, const grtMeshDesc* meshes, uint32_t n) {
+    if (!c) return 1;
+    if (n && !meshes) return fail(c, "grtSetMeshes: meshes is NULL");
+    c->h_tri9.clear(); c->h_meta.clear(); c->h_normals.clear(); c->h_faces.clear();
+    for (uint32_t m = 0; m < n; ++m) {
+        const grtMeshDesc& d = meshes[m];
+        if (d.index_count % 3) return fail(c, "grtSetMeshes: mesh %u index_count %u is not a multiple of 3", m, d.index_count);
+        const float* T = d.transform;  // glm column-major: T[4*col + row]
+        // world vertices = what an OptiX instance transform does to the GAS vertices; normals = mat3(transform) * n,
+        // NOT inverse-transpose (src/GaussianTracer.cpp:658-663).  Un-fused, glm's evaluation order.
+        std::vector<float> vw(3ull * d.vertex_count), nw(3ull * d.vertex_count);
+        for (uint32_t i = 0; i < d.vertex_count; ++i) {
+            const float x = d.vertices[3 * i], y = d.vertices[3 * i + 1], z = d.vertices[3 * i + 2];
+            const float nx = d.normals[3 * i], ny = d.normals[3 * i + 1], nz = d.normals[3 * i + 2];
+            for (int r = 0; r < 3; ++r) {
+                volatile float a = T[0 + r] * x, b = T[4 + r] * y, cc = T[8 + r] * z;
+                volatile float s1 = a + b; volatile float s2 = s1 + cc;
+                vw[3 * i + r] = s2 + T[12 + r];
+                volatile float na = T[0 + r] * nx, nb = T[4 + r] * ny, nc = T[8 + r] * nz;
+                volatile float n1 = na + nb;
+                nw[3 * i + r] = n1 + nc;
+            }
+        }
+        std::vector<uint32_t> faces(d.indices, d.indices + d.index_count);
+        for (uint32_t f = 0; f < d.index_count / 3; ++f) {
+            for (int j = 0; j < 3; ++j) {
+                const uint32_t vi = faces[3 * f + j];
+                if (vi >= d.vertex_count) return fail(c, "grtSetMeshes: mesh %u face %u references vertex %u >= %u", m, f, vi, d.vertex_count);
+                c->h_tri9.push_back(vw[3 * vi]); c->h_tri9.push_back(vw[3 * vi + 1]); c->h_tri9.push_back(vw[3 * vi + 2]);
+            }
+            c->h_meta.push_back(make_uint2(m, f));
+        }
+        c->h_normals.push_back(std::move(nw));
+        c->h_faces.push_back(std::move(faces));
+    }
+    return 0;
+}
+
+int grtBuildMeshAccel(grtContext* c, void* stream_v, uint64_t* mesh_handle_out, void** d_meshes_out) {
+    if (!c) return 1;
+    cudaStream_t stream = (cudaStream_t)stream_v;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaDeviceSynchronize());  // frames in flight may still read the old mesh arrays
+    free_mesh_accel(c);
+    if (mesh_handle_out) *mesh_handle_out = 0;
+    if (d_meshes_out) *d_meshes_out = nullptr;
+    c->info.n_mesh_triangles = 0; c->info.n_mesh_wide_nodes = 0; c->info.mesh_build_ms = 0;
+    const uint32_t nm = (uint32_t)c->h_faces.size();
+    const uint32_t nt = (uint32_t)c->h_meta.size();
+    if (nm == 0) return 0;
+    // Mesh{faces, vertex_normals}[] exactly as sendGeometryAttributesToDevice builds it (src/GaussianTracer.cpp:653-709)
+    std::vector<MeshDev> hm(nm);
+    for (uint32_t m = 0; m < nm; ++m) {
+        void *df = nullptr, *dn = nullptr;
+        CU(c, cudaMalloc(&df, std::max<size_t>(4, c->h_faces[m].size() * 4)));
+        c->mesh_allocs.push_back(df);
+        CU(c, cudaMalloc(&dn, std::max<size_t>(4, c->h_normals[m].size() * 4)));
+        c->mesh_allocs.push_back(dn);
+        CU(c, cudaMemcpyAsync(df, c->h_faces[m].data(), c->h_faces[m].size() * 4, cudaMemcpyHostToDevice, stream));
+        CU(c, cudaMemcpyAsync(dn, c->h_normals[m].data(), c->h_normals[m].size() * 4, cudaMemcpyHostToDevice, stream));
+        hm[m].faces = (uint3*)df;
+        hm[m].vertex_normals = (float3*)dn;
+    }
+    CU(c, cudaMalloc(&c->d_meshes, sizeof(MeshDev) * nm));
+    CU(c, cudaMemcpyAsync(c->d_meshes, hm.data(), sizeof(MeshDev) * nm, cudaMemcpyHostToDevice, stream));
+    if (d_meshes_out) *d_meshes_out = c->d_meshes;
+    if (nt == 0) { CU(c, cudaStreamSynchronize(stream)); return 0; }
+    cudaEvent_t e0, e1;
+    CU(c, cudaEventCreate(&e0));
+    CU(c, cudaEventCreate(&e1));
+    CU(c, cudaEventRecord(e0, stream));
+    float* d_tri9 = nullptr; uint2* d_meta = nullptr; float4 *d_lo = nullptr, *d_hi = nullptr;
+    CU(c, cudaMalloc(&d_tri9, sizeof(float) * 9ull * nt));
+    CU(c, cudaMalloc(&d_meta, sizeof(uint2) * (size_t)nt));
+    CU(c, cudaMalloc(&d_lo, sizeof(float4) * (size_t)nt));
+    CU(c, cudaMalloc(&d_hi, sizeof(float4) * (size_t)nt));
+    CU(c, cudaMemcpyAsync(d_tri9, c->h_tri9.data(), sizeof(float) * 9ull * nt, cudaMemcpyHostToDevice, stream));
+    CU(c, cudaMemcpyAsync(d_meta, c->h_meta.data(), sizeof(uint2) * (size_t)nt, cudaMemcpyHostToDevice, stream));
+    int rc = mesh_compute_boxes(d_tri9, nt, d_lo, d_hi, stream, &c->launches);
+    LbvhResult res;
+    if (!rc) rc = lbvh_build(d_lo, d_hi, nt, stream, &res, &c->launches);
+    if (!rc && res.n_live) {
+        rc = (int)cudaMalloc(&c->m_tris, sizeof(TriRec) * (size_t)res.n_live);
+        if (!rc) rc = mesh_gather(d_tri9, d_meta, res.perm, res.n_live, c->m_tris, stream, &c->launches);
+    }
+    cudaError_t es = cudaStreamSynchronize(stream);
+    cudaFree(d_tri9); cudaFree(d_meta); cudaFree(d_lo); cudaFree(d_hi); cudaFree(res.perm);
+    if (rc || es != cudaSuccess) { cudaFree(res.nodes); return fail(c, "mesh accel build failed: %s", cudaGetErrorString(rc ? (cudaError_t)rc : es)); }
+    c->m_nodes = res.nodes; c->m_count = res.n_live; c->m_nnodes = res.n_nodes;
+    if (res.n_live) {
+        AccelHeader h{};
+        h.magic = ACCEL_MAGIC_MESH; h.nodes = c->m_nodes; h.tris = c->m_tris; h.n_prims = res.n_live; h.n_nodes = res.n_nodes;
+        CU(c, cudaMalloc(&c->d_m_header, sizeof(AccelHeader)));
+        CU(c, cudaMemcpyAsync(c->d_m_header, &h, sizeof(h), cudaMemcpyHostToDevice, stream));
+    }
+    CU(c, cudaEventRecord(e1, stream));
+    CU(c, cudaStreamSynchronize(stream));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    c->info.n_mesh_triangles = res.n_live; c->info.n_mesh_wide_nodes = res.n_nodes; c->info.mesh_build_ms = ms;
+    if (mesh_handle_out) *mesh_handle_out = (uint64_t)(uintptr_t)c->d_m_header;
+    return 0;
+}
+
+// ---------------------------------------------------------------- render
+static int do_launch(grtContext* c, cudaStream_t stream, const grtParams* p, uint32_t x0, uint32_t y0, uint32_t w, uint32_t h) {
+    if (!p) return fail(c, "grtLaunch: host_params is NULL");
+    if (p->width == 0 || p->height == 0) return 0;
+    if (x0 + w > p->width || y0 + h > p->height) return fail(c, "grtLaunch: tile (%u,%u,%u,%u) outside %ux%u", x0, y0, w, h, p->width, p->height);
+    if (p->sh_degree_max > 3) return fail(c, "grtLaunch: sh_degree_max %u > 3", p->sh_degree_max);
+    // Handles are opaque device pointers owned by this context; anything else is a caller bug
+    // (the reference would hand a stale OptixTraversableHandle to optixLaunch and crash).
+    if (p->handle != 0 && p->handle != (uint64_t)(uintptr_t)c->d_p_header) return fail(c, "grtLaunch: Params.handle is not this context's particle accel");
+    if (p->mesh_handle != 0 && p->mesh_handle != (uint64_t)(uintptr_t)c->d_m_header) return fail(c, "grtLaunch: Params.mesh_handle is not this context's mesh accel");
+    if (p->mesh_handle != 0 && p->d_meshes != (void*)c->d_meshes) return fail(c, "grtLaunch: Params.d_meshes does not belong to Params.mesh_handle");
+    if (!p->output_buffer && !c->dbg_rgb32f) return fail(c, "grtLaunch: Params.output_buffer is NULL");
+    LaunchExtras ex{};
+    if (p->handle) { ex.p_nodes = c->p_nodes; ex.p_recs = c->p_recs; ex.p_sh = c->p_sh; ex.p_count = c->p_live; }
+    if (p->mesh_handle) { ex.m_nodes = c->m_nodes; ex.m_tris = c->m_tris; ex.m_count = c->m_count; }
+    ex.x0 = x0; ex.y0 = y0; ex.w = w; ex.h = h;
+    ex.rgb32f = c->dbg_rgb32f;
+    ex.trace_ids = c->dbg_trace_ids; ex.trace_counts = c->dbg_trace_counts;
+    ex.tx0 = c->tx0; ex.ty0 = c->ty0; ex.tw = c->tw; ex.th = c->th; ex.trace_max = c->trace_max;
+    ex.counters = c->d_counters;
+    CU(c, cudaEventRecord(c->ev0, stream));
+    RC(c, launch_trace(*p, ex, c->counters_on, stream));
+    CU(c, cudaEventRecord(c->ev1, stream));
+    c->ev_valid = true;
+    c->launches += 1;
+    return 0;
+}
+
+int grtLaunch(grtContext* c, void* stream, const grtParams* p) {
+    if (!c) return 1;
+    if (!p) return fail(c, "grtLaunch: host_params is NULL");
+    return do_launch(c, (cudaStream_t)stream, p, 0, 0, p->width, p->height);
+}
+int grtLaunchTile(grtContext* c, void* stream, const grtParams* p, uint32_t x0, uint32_t y0, uint32_t w, uint32_t h) {
+    if (!c) return 1;
+    return do_launch(c, (cudaStream_t)stream, p, x0, y0, w, h);
+}
+int grtLaunchBatch(grtContext* c, void* stream, const grtParams* arr, uint32_t n) {
+    if (!c) return 1;
+    if (n && !arr) return fail(c, "grtLaunchBatch: array is NULL");
+    for (uint32_t i = 0; i < n; ++i) {
+        int rc = do_launch(c, (cudaStream_t)stream, &arr[i], 0, 0, arr[i].width, arr[i].height);
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+int grtRenderHost(grtContext* c, const grtParams* p, uint8_t* host_rgb8, uint32_t y0, uint32_t h) {
+    if (!c) return 1;
+    if (!p || !host_rgb8) return fail(c, "grtRenderHost: bad argument");
+    if (h == 0) { y0 = 0; h = p->height; }
+    if (y0 + h > p->height) return fail(c, "grtRenderHost: rows [%u,%u) outside height %u", y0, y0 + h, p->height);
+    const size_t need = (size_t)p->width * p->height * 3;
+    if (need > c->frame_bytes) {
+        cudaFree(c->d_frame);
+        c->d_frame = nullptr; c->frame_bytes = 0;
+        CU(c, cudaMalloc(&c->d_frame, need));
+        c->frame_bytes = need;
+    }
+    grtParams q = *p;
+    q.output_buffer = c->d_frame;
+    if (q.mode_fisheye) CU(c, cudaMemsetAsync(c->d_frame + (size_t)3 * q.width * y0, 0, (size_t)3 * q.width * h, c->own_stream));  // GaussianTracer.cpp:510-513
+    int rc = do_launch(c, c->own_stream, &q, 0, y0, q.width, h);
+    if (rc) return rc;
+    const size_t off = (size_t)3 * q.width * y0;
+    CU(c, cudaMemcpyAsync(host_rgb8 + off, c->d_frame + off, (size_t)3 * q.width * h, cudaMemcpyDeviceToHost, c->own_stream));
+    CU(c, cudaStreamSynchronize(c->own_stream));
+    return 0;
+}
+
+// ---------------------------------------------------------------- side channels
+int grtSetDebugOutputs(grtContext* c, float* d_rgb32f, uint32_t* d_trace_ids, uint32_t* d_trace_counts, uint32_t tx0, uint32_t ty0, uint32_t tw,
+                       uint32_t th, uint32_t trace_max) {
+    if (!c) return 1;
+    c->dbg_rgb32f = d_rgb32f;
+    c->dbg_trace_ids = (tw && th && trace_max) ? d_trace_ids : nullptr;
+    c->dbg_trace_counts = d_trace_counts;
+    c->tx0 = tx0; c->ty0 = ty0; c->tw = tw; c->th = th; c->trace_max = trace_max;
+    return 0;
+}
+int grtEnableCounters(grtContext* c, int enable) { if (!c) return 1; c->counters_on = enable != 0; return 0; }
+int grtGetCounters(grtContext* c, grtCounters* out, int reset) {
+    if (!c || !out) return 1;
+    CU(c, cudaDeviceSynchronize());
+    DeviceCounters d;
+    CU(c, cudaMemcpy(&d, c->d_counters, sizeof(d), cudaMemcpyDeviceToHost));
+    out->rays = d.rays; out->segments = d.segments; out->rounds = d.rounds; out->hits_gathered = d.hits_gathered;
+    out->hits_shaded = d.hits_shaded; out->warp_nodes = d.warp_nodes; out->warp_leaf_prims = d.warp_leaf_prims;
+    out->warp_rounds = d.warp_rounds; out->stack_overflow = d.stack_overflow; out->kernel_launches = c->launches;
+    if (reset) CU(c, cudaMemset(c->d_counters, 0, sizeof(DeviceCounters)));
+    return 0;
+}
+int grtGetBuildInfo(grtContext* c, grtBuildInfo* out) { if (!c || !out) return 1; *out = c->info; return 0; }
+int grtLastLaunchMs(grtContext* c, float* ms) {
+    if (!c || !ms) return 1;
+    if (!c->ev_valid) return fail(c, "grtLastLaunchMs: nothing launched yet");
+    CU(c, cudaEventSynchronize(c->ev1));
+    CU(c, cudaEventElapsedTime(ms, c->ev0, c->ev1));
+    return 0;
+}
+
+int grtValidateAccel(grtContext* c, int which) {
+    if (!c) return 1;
+    const WideNode* dn = which ? c->m_nodes : c->p_nodes;
+    const uint32_t nn = which ? c->m_nnodes : c->p_nnodes, np = which ? c->m_count : c->p_live;
+    if (nn == 0) return np == 0 ? 0 : fail(c, "validate: %u prims but no nodes", np);
+    CU(c, cudaDeviceSynchronize());
+    std::vector<WideNode> nodes(nn);
+    CU(c, cudaMemcpy(nodes.data(), dn, sizeof(WideNode) * (size_t)nn, cudaMemcpyDeviceToHost));
+    std::vector<uint8_t> seen_prim(np, 0), seen_node(nn, 0);
+    struct Item { uint32_t node; float lo[3], hi[3]; };
+    std::vector<Item> st;
+    st.push_back(Item{0, {-INFINITY, -INFINITY, -INFINITY}, {INFINITY, INFINITY, INFINITY}});
+    seen_node[0] = 1;
+    uint64_t prim_total = 0;
+    while (!st.empty()) {
+        Item it = st.back();
+        st.pop_back();
+        const WideNode& nd = nodes[it.node];
+        for (int k = 0; k < WIDE; ++k) {
+            const uint32_t ref = nd.child[k];
+            if (ref == CHILD_EMPTY) continue;
+            const float lo[3] = {nd.lox[k], nd.loy[k], nd.loz[k]}, hi[3] = {nd.hix[k], nd.hiy[k], nd.hiz[k]};
+            for (int a = 0; a < 3; ++a) {
+                if (!(lo[a] <= hi[a])) return fail(c, "validate: node %u child %d has an inverted/NaN box", it.node, k);
+                if (lo[a] < it.lo[a] || hi[a] > it.hi[a]) return fail(c, "validate: node %u child %d box escapes its parent", it.node, k);
+            }
+            if (ref & CHILD_LEAF) {
+                const uint32_t start = ref & 0x0FFFFFFFu, cnt = ((ref >> 28) & 7u) + 1u;
+                if (cnt > (uint32_t)LEAF_MAX) return fail(c, "validate: leaf run of %u > LEAF_MAX", cnt);
+                for (uint32_t j = start; j < start + cnt; ++j) {
+                    if (j >= np) return fail(c, "validate: leaf references record %u >= %u", j, np);
+                    if (seen_prim[j]) return fail(c, "validate: record %u referenced twice", j);
+                    seen_prim[j] = 1;
+                    ++prim_total;
+                }
+            } else {
+                if (ref >= nn) return fail(c, "validate: child node %u >= %u", ref, nn);
+                if (seen_node[ref]) return fail(c, "validate: node %u referenced twice", ref);
+                seen_node[ref] = 1;
+                Item ch{ref, {lo[0], lo[1], lo[2]}, {hi[0], hi[1], hi[2]}};
+                st.push_back(ch);
+            }
+        }
+    }
+    if (prim_total != np) return fail(c, "validate: %llu of %u records reachable", (unsigned long long)prim_total, np);
+    // leaf boxes must contain their records: checked for particles via the record centre (mu)
+    if (!which && np) {
+        std::vector<PRec> recs(np);
+        CU(c, cudaMemcpy(recs.data(), c->p_recs, sizeof(PRec) * (size_t)np, cudaMemcpyDeviceToHost));
+        for (uint32_t n = 0; n < nn; ++n)
+            for (int k = 0; k < WIDE; ++k) {
+                const uint32_t ref = nodes[n].child[k];
+                if (ref == CHILD_EMPTY || !(ref & CHILD_LEAF)) continue;
+                const uint32_t start = ref & 0x0FFFFFFFu, cnt = ((ref >> 28) & 7u) + 1u;
+                for (uint32_t j = start; j < start + cnt; ++j) {
+                    const float mu[3] = {recs[j].q2.y, recs[j].q2.z, recs[j].q2.w};
+                    const float lo[3] = {nodes[n].lox[k], nodes[n].loy[k], nodes[n].loz[k]}, hi[3] = {nodes[n].hix[k], nodes[n].hiy[k], nodes[n].hiz[k]};
+                    for (int a = 0; a < 3; ++a)
+                        if (mu[a] < lo[a] || mu[a] > hi[a]) return fail(c, "validate: record %u centre outside its leaf box", j);
+                }
+            }
+    }
+    return 0;
+}
+
+int grtDebugRadixSort(grtContext* c, uint64_t* host_keys, uint32_t* host_vals, uint64_t n) {
+    if (!c) return 1;
+    if (n == 0) return 0;
+    if (n >= (1ull << 31)) return fail(c, "grtDebugRadixSort: n too large");
+    CU(c, cudaSetDevice(c->device));
+    uint64_t *k0 = nullptr, *k1 = nullptr; uint32_t *v0 = nullptr, *v1 = nullptr;
+    CU(c, cudaMalloc(&k0, 8 * n)); CU(c, cudaMalloc(&k1, 8 * n)); CU(c, cudaMalloc(&v0, 4 * n)); CU(c, cudaMalloc(&v1, 4 * n));
+    CU(c, cudaMemcpy(k0, host_keys, 8 * n, cudaMemcpyHostToDevice));
+    CU(c, cudaMemcpy(v0, host_vals, 4 * n, cudaMemcpyHostToDevice));
+    bool in_tmp = false;
+    int rc = radix_sort_pairs(k0, k1, v0, v1, (uint32_t)n, nullptr, &c->launches, &in_tmp);
+    if (!rc) {
+        rc = (int)cudaMemcpy(host_keys, in_tmp ? k1 : k0, 8 * n, cudaMemcpyDeviceToHost);
+        if (!rc) rc = (int)cudaMemcpy(host_vals, in_tmp ? v1 : v0, 4 * n, cudaMemcpyDeviceToHost);
+    }
+    cudaFree(k0); cudaFree(k1); cudaFree(v0); cudaFree(v1);
+    if (rc) return fail(c, "grtDebugRadixSort failed: %s", cudaGetErrorString((cudaError_t)rc));
+    return 0;
+}
+
+}  // extern "C"

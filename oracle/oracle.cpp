@@ -354,6 +354,7 @@ struct PixelCtx {
     Counters* cnt;
     uint32_t flags;
     uint32_t hg_pixel;
+    uint32_t last_id;  // particle whose face hit defines the current re-launch point
     // trace
     uint32_t* trace_ids;
     uint32_t trace_max, trace_n;
@@ -381,7 +382,7 @@ inline void offer(PixelCtx& c, HitPayload* buf, uint32_t K, const Proxy& P, f3 o
     }
     for (int k = 0; k < 2; ++k) {
         float t = t2[k];
-        if (ulp_close(t, tmin, 4)) c.flags |= ORC_FLAG_TIE;  // a face hit sitting on the re-launch point
+        if (P.id != c.last_id && ulp_close(t, tmin, 4)) c.flags |= ORC_FLAG_TIE;  // another proxy's face hit sitting on the re-launch point
         if (t > tmin && t < cur_tmax) anyhit(buf, K, P.id, t, cur_tmax);
     }
 }
@@ -467,6 +468,7 @@ void trace(PixelCtx& c, RayData& rayData, f3 ray_o, f3 ray_d, float t_min, float
     HitPayload buf[64];
     float prev_t = -1.0f;
     c.cnt->segments++;
+    c.last_id = InvalidParticleId;
     auto tcheck = [&](float T) {
         if (fabsf(T - params.minTransmittance) <= 1e-6f) c.flags |= ORC_FLAG_TRANSMIT;
         return T > params.minTransmittance;
@@ -483,6 +485,7 @@ void trace(PixelCtx& c, RayData& rayData, f3 ray_o, f3 ray_d, float t_min, float
                 c.cnt->hg++;
                 c.hg_pixel++;
                 if (c.trace_ids) { if (c.trace_n < c.trace_max) c.trace_ids[c.trace_n] = hit.particleId; c.trace_n++; }
+                if (hit.distance >= rayLastHitDistance) c.last_id = hit.particleId;
                 rayLastHitDistance = fmaxf(hit.distance, rayLastHitDistance);
                 float hitAlpha = computeResponse(currParticle, ray_o, ray_d);
                 hitAlpha = fminf(0.99f, hitAlpha * currParticle.opacity);
@@ -751,7 +754,7 @@ int orc_render(const OrcScene* S, const OrcRenderArgs* A, OrcStats* stats) {
             for (uint32_t x = x0; x < x0 + w; ++x) {
                 PixelCtx c;
                 c.S = S; c.A = A; c.prm = &prm; c.cnt = &cnts[tid];
-                c.flags = 0; c.hg_pixel = 0;
+                c.flags = 0; c.hg_pixel = 0; c.last_id = InvalidParticleId;
                 c.trace_ids = nullptr; c.trace_max = 0; c.trace_n = 0;
                 size_t pix = (size_t)y * prm.width + x;
                 int32_t slot = trace_slot.empty() ? -1 : trace_slot[pix];

@@ -4,6 +4,7 @@
  * (U,V,W frame).  Output: oracle/_ref/libref_host.so (git-ignored; travels to the GPU box).
  * TEST INFRASTRUCTURE ONLY: used to pin our own PLY loader / camera against the reference's code.
  */
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <string>
@@ -25,6 +26,10 @@ void* ref_load_ply(const char* path, unsigned long long* n_out, float center_out
         float3 c = gd.getCenter();
         center_out[0] = c.x; center_out[1] = c.y; center_out[2] = c.z;
         return buf;
+    } catch (const std::exception& e) {
+        fprintf(stderr, "ref_load_ply: %s\n", e.what());
+        *n_out = 0;
+        return nullptr;
     } catch (...) {
         *n_out = 0;
         return nullptr;
