@@ -311,7 +311,7 @@ struct Bvh {
         return me;
     }
 };
-inline bool box_hit(const Box& b, f3 o, f3 inv, float tmin, float tmax) {
+inline bool box_hit(const Box& b, f3 o, f3 inv, float tmin, float tmax, float* t_enter = nullptr) {
     float t0 = tmin, t1 = tmax;
     const float oo[3] = {o.x, o.y, o.z}, ii[3] = {inv.x, inv.y, inv.z};
     for (int k = 0; k < 3; ++k) {
@@ -320,6 +320,7 @@ inline bool box_hit(const Box& b, f3 o, f3 inv, float tmin, float tmax) {
         t0 = fmaxf(t0, fminf(a, c));
         t1 = fminf(t1, fmaxf(a, c));
     }
+    if (t_enter) *t_enter = t0;
     return t0 <= t1 * 1.00001f + 1e-7f;
 }
 
@@ -399,18 +400,26 @@ void traceGPs(PixelCtx& c, HitPayload* buf, uint32_t K, f3 o, f3 d, float tmin, 
     }
     if (S.bvh.nodes.empty()) return;
     f3 inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
-    uint32_t stack[128];
+    uint32_t stack[256];
     int sp = 0;
+    if (!box_hit(S.bvh.nodes[0].b, o, inv, tmin, cur_tmax)) return;
     stack[sp++] = 0;
     while (sp) {
         const BvhNode& n = S.bvh.nodes[stack[--sp]];
         c.cnt->nodes++;
-        if (!box_hit(n.b, o, inv, tmin, cur_tmax)) continue;
         if (n.count) {
+            if (!box_hit(n.b, o, inv, tmin, cur_tmax)) continue;  // tmax may have shrunk since the push
             for (uint32_t i = 0; i < n.count; ++i) offer(c, buf, K, S.proxies[S.bvh.prims[n.first + i]], o, d, tmin, cur_tmax);
         } else {
-            stack[sp++] = n.right;
-            stack[sp++] = n.left;
+            // near child first so that the k-buffer bound tightens early (any order gives the same K smallest)
+            float tl, tr;
+            const bool hl = box_hit(S.bvh.nodes[n.left].b, o, inv, tmin, cur_tmax, &tl);
+            const bool hr = box_hit(S.bvh.nodes[n.right].b, o, inv, tmin, cur_tmax, &tr);
+            if (hl && hr) {
+                if (tl <= tr) { stack[sp++] = n.right; stack[sp++] = n.left; }
+                else { stack[sp++] = n.left; stack[sp++] = n.right; }
+            } else if (hl) stack[sp++] = n.left;
+            else if (hr) stack[sp++] = n.right;
         }
     }
 }
@@ -470,7 +479,7 @@ void trace(PixelCtx& c, RayData& rayData, f3 ray_o, f3 ray_d, float t_min, float
     c.cnt->segments++;
     c.last_id = InvalidParticleId;
     auto tcheck = [&](float T) {
-        if (fabsf(T - params.minTransmittance) <= 1e-6f) c.flags |= ORC_FLAG_TRANSMIT;
+        if (fabsf(T - params.minTransmittance) <= 5e-8f) c.flags |= ORC_FLAG_TRANSMIT;
         return T > params.minTransmittance;
     };
     while ((rayLastHitDistance <= t_max) && tcheck(rayTransmittance)) {
@@ -489,7 +498,7 @@ void trace(PixelCtx& c, RayData& rayData, f3 ray_o, f3 ray_d, float t_min, float
                 rayLastHitDistance = fmaxf(hit.distance, rayLastHitDistance);
                 float hitAlpha = computeResponse(currParticle, ray_o, ray_d);
                 hitAlpha = fminf(0.99f, hitAlpha * currParticle.opacity);
-                if (fabsf(hitAlpha - params.alpha_min) <= 1e-6f) c.flags |= ORC_FLAG_ALPHA;
+                if (fabsf(hitAlpha - params.alpha_min) <= 5e-7f) c.flags |= ORC_FLAG_ALPHA;
                 if (params.alpha_min < hitAlpha) {
                     f3 hitRadiance = computeRadiance(currParticle, normalize(ray_d), params.sh_degree_max);
                     radiance += rayTransmittance * hitRadiance * hitAlpha;

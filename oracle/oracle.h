@@ -65,8 +65,8 @@ typedef struct OrcScene OrcScene;
 
 /* flags in the per-pixel flag image */
 #define ORC_FLAG_TIE 1u        /* two gathered face hits within 4 ulp, or a hit within 4 ulp of a segment bound */
-#define ORC_FLAG_ALPHA 2u      /* |alpha - alpha_min| <= 1e-6 for some hit */
-#define ORC_FLAG_TRANSMIT 4u   /* |T - minTransmittance| <= 1e-6 at some check */
+#define ORC_FLAG_ALPHA 2u      /* |alpha - alpha_min| <= 5e-7 for some hit */
+#define ORC_FLAG_TRANSMIT 4u   /* |T - minTransmittance| <= 5e-8 at some check */
 #define ORC_FLAG_MESH 8u       /* mesh closest hit ambiguous (two triangles within 4 ulp) */
 
 /* Scene = particles (+ proxy transform of GaussianTracer.cpp:297-317 with alpha_min_build) + CPU BVH. */
