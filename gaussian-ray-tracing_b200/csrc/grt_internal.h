@@ -8,7 +8,7 @@
 namespace grt {
 
 constexpr int WIDE = 8;            // children per wide node
-constexpr int LEAF_MAX = 4;        // proxies (or triangles) per leaf child
+constexpr int LEAF_MAX = 1;        // proxies (or triangles) per leaf child
 constexpr uint32_t CHILD_EMPTY = 0xFFFFFFFFu;
 constexpr uint32_t CHILD_LEAF = 0x80000000u;  // leaf: CHILD_LEAF | (count-1) << 28 | start (28 bits)
 constexpr uint32_t INVALID_ID = 0xFFFFFFFFu;
@@ -60,7 +60,7 @@ struct MeshDev {
 
 struct DeviceCounters {
     unsigned long long rays, segments, rounds, hits_gathered, hits_shaded, warp_nodes, warp_leaf_prims, warp_rounds,
-        stack_overflow;
+        stack_overflow, warp_prims_hit, warp_consume_iters, lanes_repass, order_violations, warp_dfs_fallbacks;
 };
 
 // Extra kernel arguments next to the 144-byte Params.

@@ -82,6 +82,11 @@ typedef struct grtCounters {
     uint64_t warp_rounds;
     uint64_t stack_overflow;  /* must stay 0 */
     uint64_t kernel_launches; /* launches issued by this context since creation (all kernels) */
+    uint64_t warp_prims_hit;  /* proxy records that at least one lane of the packet hit */
+    uint64_t warp_consume_iters; /* warp iterations of the shading loop (SIMD efficiency = h_g / (32 x this)) */
+    uint64_t lanes_repass;    /* rays that needed another traversal pass because their pending buffer overflowed */
+    uint64_t order_violations;/* face hits found behind the already composited front; must stay 0 */
+    uint64_t warp_dfs_fallbacks; /* packets whose best-first queue filled up and that redid the pass depth-first */
 } grtCounters;
 
 typedef struct grtContext grtContext;
