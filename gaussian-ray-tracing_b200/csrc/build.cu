@@ -308,22 +308,35 @@ __global__ void collapse_kernel(BinTree T, const uint2* __restrict__ q_in, uint3
     int ns = 2;
     slots[0] = T.left[b];
     slots[1] = T.right[b];
+    // Open the largest-area child until the node is full.  A subtree of more than WIDE records is split into its
+    // two binary children; a smaller one is only opened if ALL its records fit into the free slots (it is then
+    // flattened into single-record leaf children), so that the bottom of the tree is made of well-filled nodes
+    // instead of chains of 2- and 3-child nodes.
     while (ns < WIDE) {
         int best = -1;
         float bestA = -1.0f;
         for (int k = 0; k < ns; ++k) {
             const uint32_t id = slots[k];
-            if (id < T.n - 1 && T.count(id) > (uint32_t)LEAF_MAX) {
-                const float4 a = T.blo[id], c = T.bhi[id];
-                const float ex = c.x - a.x, ey = c.y - a.y, ez = c.z - a.z;
-                const float area = ex * ey + ey * ez + ez * ex;
-                if (area > bestA) { bestA = area; best = k; }
-            }
+            if (id >= T.n - 1) continue;
+            const uint32_t c = T.count(id);
+            if (c <= (uint32_t)LEAF_MAX) continue;
+            if (LEAF_MAX == 1 && c <= (uint32_t)WIDE && ns - 1 + (int)c > WIDE) continue;
+            const float4 a = T.blo[id], d = T.bhi[id];
+            const float ex = d.x - a.x, ey = d.y - a.y, ez = d.z - a.z;
+            const float area = ex * ey + ey * ez + ez * ex;
+            if (area > bestA) { bestA = area; best = k; }
         }
         if (best < 0) break;
         const uint32_t id = slots[best];
-        slots[best] = T.left[id];
-        slots[ns++] = T.right[id];
+        const uint32_t c = T.count(id);
+        if (LEAF_MAX == 1 && c <= (uint32_t)WIDE) {
+            const uint32_t s0 = T.start(id);
+            slots[best] = T.n - 1 + s0;
+            for (uint32_t k = 1; k < c; ++k) slots[ns++] = T.n - 1 + s0 + k;
+        } else {
+            slots[best] = T.left[id];
+            slots[ns++] = T.right[id];
+        }
     }
     WideNode* nd = &nodes[w];
     for (int k = 0; k < WIDE; ++k) {
