@@ -108,9 +108,10 @@ def load_libgrt():
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(LIBGRT_PATH):
-        raise GrtError(f"{LIBGRT_PATH} is missing: run `make -C {_HERE}` (or __graft_entry__.build()); there is no fallback path")
-    lib = C.CDLL(LIBGRT_PATH)
+    path = os.environ.get("GRT_LIBGRT", LIBGRT_PATH)  # tuning builds (tools/build_variants.sh); same ABI, still CUDA-only
+    if not os.path.exists(path):
+        raise GrtError(f"{path} is missing: run `make -C {_HERE}` (or __graft_entry__.build()); there is no fallback path")
+    lib = C.CDLL(path)
     vp, u32, u64, i32, f32 = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int, C.c_float
     sig = {
         "grtCreate": [i32, C.POINTER(vp)],
