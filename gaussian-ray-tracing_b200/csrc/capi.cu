@@ -453,7 +453,7 @@ int grtGetCounters(grtContext* c, grtCounters* out, int reset) {
     out->hits_shaded = d.hits_shaded; out->warp_nodes = d.warp_nodes; out->warp_leaf_prims = d.warp_leaf_prims;
     out->warp_rounds = d.warp_rounds; out->stack_overflow = d.stack_overflow; out->kernel_launches = c->launches;
     out->warp_prims_hit = d.warp_prims_hit; out->warp_consume_iters = d.warp_consume_iters; out->lanes_repass = d.lanes_repass;
-    out->order_violations = d.order_violations; out->warp_dfs_fallbacks = d.warp_dfs_fallbacks;
+    out->order_violations = d.order_violations; out->warp_dfs_fallbacks = d.warp_dfs_fallbacks; out->warp_candidate_iters = d.warp_candidate_iters;
     if (reset) CU(c, cudaMemset(c->d_counters, 0, sizeof(DeviceCounters)));
     return 0;
 }

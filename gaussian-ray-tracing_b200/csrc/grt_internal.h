@@ -60,7 +60,7 @@ struct MeshDev {
 
 struct DeviceCounters {
     unsigned long long rays, segments, rounds, hits_gathered, hits_shaded, warp_nodes, warp_leaf_prims, warp_rounds,
-        stack_overflow, warp_prims_hit, warp_consume_iters, lanes_repass, order_violations, warp_dfs_fallbacks;
+        stack_overflow, warp_prims_hit, warp_consume_iters, lanes_repass, order_violations, warp_dfs_fallbacks, warp_candidate_iters;
 };
 
 // Extra kernel arguments next to the 144-byte Params.
