@@ -156,9 +156,16 @@ def camera_uvw(eye, lookat, up, fov_y_deg: float, aspect: float):
     return U.astype(np.float32), V.astype(np.float32), W.astype(np.float32)
 
 
+def gaussian_center(particles: np.ndarray) -> np.ndarray:
+    """GaussianData::getCenter (src/GaussianData.cpp:140-152): sequential float32 sums, then one division."""
+    pos = np.ascontiguousarray(particles[:, 0:3], dtype=np.float32)
+    sums = np.add.accumulate(pos, axis=0, dtype=np.float32)[-1]
+    return (sums / np.float32(len(pos))).astype(np.float32)
+
+
 def default_camera(particles: np.ndarray):
     """GUI defaults (src/gui.cpp:50-56): eye (0,0,3), lookat = mean particle position, up (0,1,0), fovY 60."""
-    center = particles[:, 0:3].astype(np.float64).mean(axis=0).astype(np.float32) if len(particles) else _f32([0, 0, 0])
+    center = gaussian_center(particles) if len(particles) else _f32([0, 0, 0])
     return dict(eye=_f32([0, 0, 3]), lookat=center, up=_f32([0, 1, 0]), fov_y=60.0)
 
 

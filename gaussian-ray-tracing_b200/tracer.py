@@ -88,7 +88,8 @@ class GaussianTracer:
         self.params.width, self.params.height = int(width), int(height)
 
     def getGaussianCenter(self):
-        return self.particles[:, 0:3].astype(np.float64).mean(axis=0).astype(np.float32)
+        from .scene import gaussian_center
+        return gaussian_center(self.particles)
 
     def initializeOptix(self):
         """Keeps the reference name; uploads the particles and builds the LBVH on the device."""
