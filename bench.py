@@ -135,14 +135,14 @@ def main():
     P.handle, P.d_particles = handle, dpart
     frame = torch.zeros((H, W, 3), dtype=torch.uint8, device="cuda")
     P.output_buffer = frame.data_ptr()
-    gathered = [torch.empty_like(frame) for _ in range(world)] if (world > 1 and rank == 0) else None
+    part = importlib.import_module("gaussian-ray-tracing_b200.partition")
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")  # > 126 MB L2
     rays = W * H
 
     def step():
         ctx.launch(P)  # default stream == torch's current stream
         if world > 1:
-            dist.gather(frame, gathered, dst=0)
+            part.gather_frames(frame, rank, world)
 
     # one counted pass (separate kernel variant, outside every timed region) for h_g / h_s
     ctx.enable_counters(True)
@@ -172,7 +172,7 @@ def main():
         ctx.launch(P)
         b.record()
         if world > 1:
-            dist.gather(frame, gathered, dst=0)
+            part.gather_frames(frame, rank, world)  # camera-batch partition: the only exchange is the framebuffer gather
         c.record()
     torch.cuda.synchronize()
     if world > 1:
@@ -218,6 +218,10 @@ def main():
         bytes_per_ray = 44.0 * hg + 12.0 * (w["deg"] + 1) ** 2 * hs + 3.0
         k_ms = float(np.mean(kernel_ms))
         achieved = rays * bytes_per_ray / (k_ms * 1e-3) / 1e9
+        traffic = None  # dram__bytes_read.sum + dram__bytes_write.sum of trace_kernel from the committed ncu capture
+        ncu_path = os.path.join(ROOT, "profiles", "r1_trace_kernel_ncu.json")
+        if os.path.exists(ncu_path) and not args.fisheye:
+            traffic = json.load(open(ncu_path)).get("dram_bytes_per_launch")
         line = {
             "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
@@ -226,12 +230,14 @@ def main():
                                     % ("fisheye" if args.fisheye else "pinhole")),
                        "n_live": int(info["n_live"]), "wide_nodes": int(info["n_wide_nodes"]), "bvh_build_ms": float(info["build_ms"]),
                        "l2": "256 MB flush write between timed iterations; scene arrays 256 MB + BVH > 126 MB L2",
+                       "partition": "scene+BVH replicated per GPU, one camera per rank, frames gathered to rank 0 (NCCL)" if world > 1 else "single GPU",
                        "hits_gathered_per_ray": hg, "hits_shaded_per_ray": hs, "rounds_per_ray": cnt["rounds"] / cnt["rays"]},
             "kernel_ms": k_ms,
             "e2e": {"value": e2e, "unit": "Mrays/s", "h2d_bytes_per_step": 144, "d2h_bytes_per_step": rays * 3},
             "gpu_launches": int(launches),
             "clocks": sampler.result(),
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                         "algorithmic_bytes_per_launch": rays * bytes_per_ray,
                          "peak_source": peak_src, "algorithmic_bytes_per_ray": bytes_per_ray, "kernel": "trace_kernel<false>"},
         }
         if world == 1 and not args.no_cpu_baseline:
