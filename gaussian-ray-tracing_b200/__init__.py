@@ -88,7 +88,7 @@ class GrtCounters(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in (
         "rays", "segments", "rounds", "hits_gathered", "hits_shaded", "warp_nodes", "warp_leaf_prims",
         "warp_rounds", "stack_overflow", "kernel_launches", "warp_prims_hit", "warp_consume_iters", "lanes_repass",
-        "order_violations", "warp_dfs_fallbacks", "warp_candidate_iters")]
+        "order_violations", "warp_dfs_fallbacks", "warp_candidate_iters")] + [("dbg", C.c_uint64 * 8)]
 
 
 # every symbol include/grt.h declares (tests check that the .so exports all of them)
@@ -284,7 +284,9 @@ class Context:
     def counters(self, reset=False) -> dict:
         c = GrtCounters()
         self._ck(self.lib.grtGetCounters(self.h, C.byref(c), int(reset)))
-        return {n: int(getattr(c, n)) for n, _ in GrtCounters._fields_}
+        d = {n: int(getattr(c, n)) for n, _ in GrtCounters._fields_ if n != "dbg"}
+        d["dbg"] = [int(v) for v in c.dbg]
+        return d
 
     def build_info(self) -> dict:
         b = GrtBuildInfo()

@@ -52,6 +52,8 @@ struct grtContext {
     uint32_t tx0 = 0, ty0 = 0, tw = 0, th = 0, trace_max = 0;
     bool counters_on = false;
     DeviceCounters* d_counters = nullptr;
+    uint32_t* d_tile_counter = nullptr;
+    int sm_count = 0;
     // e2e frame
     uint8_t* d_frame = nullptr;
     size_t frame_bytes = 0;
@@ -112,7 +114,8 @@ int grtCreate(int device, grtContext** ctx_out) {
     if (prop.major < 10) return fail(nullptr, "grtCreate: device %d is sm_%d%d; libgrt is built for sm_100a only", device, prop.major, prop.minor);
     grtContext* c = new grtContext();
     c->device = device;
-    if (cudaMalloc(&c->d_counters, sizeof(DeviceCounters)) != cudaSuccess || cudaMemset(c->d_counters, 0, sizeof(DeviceCounters)) != cudaSuccess ||
+    c->sm_count = prop.multiProcessorCount;
+    if (cudaMalloc(&c->d_tile_counter, sizeof(uint32_t)) != cudaSuccess || cudaMalloc(&c->d_counters, sizeof(DeviceCounters)) != cudaSuccess || cudaMemset(c->d_counters, 0, sizeof(DeviceCounters)) != cudaSuccess ||
         cudaStreamCreate(&c->own_stream) != cudaSuccess || cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess) {
         delete c;
         return fail(nullptr, "grtCreate: device allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
@@ -127,7 +130,7 @@ int grtDestroy(grtContext* c) {
     cudaDeviceSynchronize();
     free_particle_accel(c);
     free_mesh_accel(c);
-    cudaFree(c->d_particles); cudaFree(c->d_s); cudaFree(c->d_counters); cudaFree(c->d_frame);
+    cudaFree(c->d_particles); cudaFree(c->d_s); cudaFree(c->d_counters); cudaFree(c->d_tile_counter); cudaFree(c->d_frame);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
@@ -383,8 +386,10 @@ static int do_launch(grtContext* c, cudaStream_t stream, const grtParams* p, uin
     ex.trace_ids = c->dbg_trace_ids; ex.trace_counts = c->dbg_trace_counts;
     ex.tx0 = c->tx0; ex.ty0 = c->ty0; ex.tw = c->tw; ex.th = c->th; ex.trace_max = c->trace_max;
     ex.counters = c->d_counters;
+    ex.tile_counter = c->d_tile_counter;
+    CU(c, cudaMemsetAsync(c->d_tile_counter, 0, sizeof(uint32_t), stream));
     CU(c, cudaEventRecord(c->ev0, stream));
-    RC(c, launch_trace(*p, ex, c->counters_on, stream));
+    RC(c, launch_trace(*p, ex, c->counters_on, stream, c->sm_count));
     CU(c, cudaEventRecord(c->ev1, stream));
     c->ev_valid = true;
     c->launches += 1;
@@ -454,6 +459,7 @@ int grtGetCounters(grtContext* c, grtCounters* out, int reset) {
     out->warp_rounds = d.warp_rounds; out->stack_overflow = d.stack_overflow; out->kernel_launches = c->launches;
     out->warp_prims_hit = d.warp_prims_hit; out->warp_consume_iters = d.warp_consume_iters; out->lanes_repass = d.lanes_repass;
     out->order_violations = d.order_violations; out->warp_dfs_fallbacks = d.warp_dfs_fallbacks; out->warp_candidate_iters = d.warp_candidate_iters;
+    for (int k = 0; k < 8; ++k) out->dbg[k] = d.dbg[k];
     if (reset) CU(c, cudaMemset(c->d_counters, 0, sizeof(DeviceCounters)));
     return 0;
 }

@@ -61,6 +61,7 @@ struct MeshDev {
 struct DeviceCounters {
     unsigned long long rays, segments, rounds, hits_gathered, hits_shaded, warp_nodes, warp_leaf_prims, warp_rounds,
         stack_overflow, warp_prims_hit, warp_consume_iters, lanes_repass, order_violations, warp_dfs_fallbacks, warp_candidate_iters;
+    unsigned long long dbg[8];  // free-form experiment counters (tools/prof_trace.py prints them)
 };
 
 // Extra kernel arguments next to the 144-byte Params.
@@ -78,6 +79,7 @@ struct LaunchExtras {
     uint32_t* trace_counts;
     uint32_t tx0, ty0, tw, th, trace_max;
     DeviceCounters* counters;
+    uint32_t* tile_counter;  // persistent-warp scheduler: next 8x4 tile to hand out (zeroed before the launch)
 };
 
 // ---- generic LBVH builder (build.cu) ----
@@ -109,6 +111,6 @@ int mesh_gather(const float* d_tri9, const uint2* d_meta, const uint32_t* d_perm
                 cudaStream_t stream, unsigned long long* launches);
 
 // trace kernel (trace.cu)
-int launch_trace(const grtParams& p, const LaunchExtras& ex, bool counters, cudaStream_t stream);
+int launch_trace(const grtParams& p, const LaunchExtras& ex, bool counters, cudaStream_t stream, int sm_count);
 
 }  // namespace grt

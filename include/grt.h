@@ -88,6 +88,7 @@ typedef struct grtCounters {
     uint64_t order_violations;/* face hits found behind the already composited front; must stay 0 */
     uint64_t warp_dfs_fallbacks; /* packets whose best-first queue filled up and that redid the pass depth-first */
     uint64_t warp_candidate_iters; /* warp iterations of the per-ray exact proxy test loop */
+    uint64_t dbg[8];          /* free-form profiling counters of the counting kernel variant (meaning: DESIGN.md) */
 } grtCounters;
 
 typedef struct grtContext grtContext;
