@@ -97,7 +97,7 @@ GRT_SYMBOLS = [
     "grtBuildMeshAccel", "grtLaunch", "grtLaunchTile", "grtLaunchBatch", "grtRenderHost", "grtSetDebugOutputs",
     "grtEnableCounters", "grtGetCounters", "grtGetBuildInfo", "grtValidateAccel", "grtLastLaunchMs", "grtMalloc",
     "grtFree", "grtMallocHost", "grtFreeHost", "grtMemcpyDtoH", "grtMemcpyHtoD", "grtMemset", "grtStreamCreate",
-    "grtStreamDestroy", "grtStreamSynchronize", "grtDebugRadixSort",
+    "grtStreamDestroy", "grtStreamSynchronize", "grtDebugRadixSort", "grtSetParticlesRaw", "grtLoadPly", "grtGetParticles",
 ]
 
 _lib = None
@@ -141,6 +141,9 @@ def load_libgrt():
         "grtStreamDestroy": [vp, vp],
         "grtStreamSynchronize": [vp, vp],
         "grtDebugRadixSort": [vp, vp, vp, u64],
+        "grtSetParticlesRaw": [vp, vp, u64, u32, C.POINTER(u32), f32],
+        "grtLoadPly": [vp, C.c_char_p, f32, C.POINTER(u64), C.POINTER(f32)],
+        "grtGetParticles": [vp, vp, u64],
     }
     for name, args in sig.items():
         fn = getattr(lib, name)
@@ -220,6 +223,26 @@ class Context:
             raise GrtError("particles must be (n, 59) float32")
         n = particles.shape[0] if particles.size else 0
         self._ck(self.lib.grtSetParticles(self.h, _np_ptr(particles) if n else None, n, alpha_min))
+
+    def set_particles_raw(self, rows: np.ndarray, prop_offsets, alpha_min: float = 0.01):
+        """rows: (n, stride_bytes) uint8 or (n, k) float32 raw PLY vertex rows; prop_offsets: 59 byte offsets
+        (x y z scale_0-2 rot_0-3 opacity f_dc_0-2 f_rest_0-44).  Activation runs on the device (csrc/ingest.cu)."""
+        rows = np.ascontiguousarray(rows)
+        n = rows.shape[0]
+        stride = rows.strides[0] if n else 236
+        off = (C.c_uint32 * 59)(*[int(o) for o in prop_offsets])
+        self._ck(self.lib.grtSetParticlesRaw(self.h, _np_ptr(rows) if n else None, n, stride, off, alpha_min))
+
+    def load_ply(self, path: str, alpha_min: float = 0.01):
+        """GaussianData(path) on the device: returns (vertex count, centre as float32[3])."""
+        n, cen = C.c_uint64(), (C.c_float * 3)()
+        self._ck(self.lib.grtLoadPly(self.h, path.encode(), alpha_min, C.byref(n), cen))
+        return int(n.value), np.array(list(cen), np.float32)
+
+    def get_particles(self, n: int) -> np.ndarray:
+        out = np.empty((n, PARTICLE_FLOATS), np.float32)
+        self._ck(self.lib.grtGetParticles(self.h, _np_ptr(out) if n else None, n))
+        return out
 
     def build_particle_accel(self, stream=None):
         handle, dpart = C.c_uint64(), C.c_void_p()

@@ -8,6 +8,11 @@
 #include <string>
 #include <vector>
 
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
 #include "grt_internal.h"
 
 using namespace grt;
@@ -211,6 +216,160 @@ int grtSetParticles(grtContext* c, const void* host_particles, uint64_t n, float
     CU(c, cudaMalloc(&c->d_s, n * sizeof(float)));
     CU(c, cudaMemcpy(c->d_particles, host_particles, n * 236ull, cudaMemcpyHostToDevice));
     CU(c, cudaMemcpy(c->d_s, s.data(), n * sizeof(float), cudaMemcpyHostToDevice));
+    return 0;
+}
+
+// ---------------------------------------------------------------- device-side PLY ingest
+static const char* const kPlyProps[59] = {
+    "x", "y", "z", "scale_0", "scale_1", "scale_2", "rot_0", "rot_1", "rot_2", "rot_3", "opacity", "f_dc_0", "f_dc_1", "f_dc_2",
+    "f_rest_0", "f_rest_1", "f_rest_2", "f_rest_3", "f_rest_4", "f_rest_5", "f_rest_6", "f_rest_7", "f_rest_8", "f_rest_9",
+    "f_rest_10", "f_rest_11", "f_rest_12", "f_rest_13", "f_rest_14", "f_rest_15", "f_rest_16", "f_rest_17", "f_rest_18", "f_rest_19",
+    "f_rest_20", "f_rest_21", "f_rest_22", "f_rest_23", "f_rest_24", "f_rest_25", "f_rest_26", "f_rest_27", "f_rest_28", "f_rest_29",
+    "f_rest_30", "f_rest_31", "f_rest_32", "f_rest_33", "f_rest_34", "f_rest_35", "f_rest_36", "f_rest_37", "f_rest_38", "f_rest_39",
+    "f_rest_40", "f_rest_41", "f_rest_42", "f_rest_43", "f_rest_44"};
+
+int grtSetParticlesRaw(grtContext* c, const void* host_rows, uint64_t n, uint32_t row_stride, const uint32_t* off59, float alpha_min) {
+    if (!c) return 1;
+    if (n && (!host_rows || !off59)) return fail(c, "grtSetParticlesRaw: NULL argument");
+    if (n >= (1ull << 28)) return fail(c, "grtSetParticlesRaw: %llu particles exceed the 2^28 limit", (unsigned long long)n);
+    if (n && (row_stride < 59 * 4 || row_stride > 1024)) return fail(c, "grtSetParticlesRaw: row stride %u outside [236, 1024]", row_stride);
+    PlyLayout L{};
+    L.stride = row_stride;
+    L.aligned = (row_stride & 3u) == 0;
+    for (int k = 0; k < 59 && n; ++k) {
+        if (off59[k] + 4u > row_stride) return fail(c, "grtSetParticlesRaw: property %s at byte %u does not fit a %u-byte row", kPlyProps[k], off59[k], row_stride);
+        L.off[k] = off59[k];
+        if (off59[k] & 3u) L.aligned = 0;
+    }
+    CU(c, cudaSetDevice(c->device));
+    free_particle_accel(c);
+    cudaFree(c->d_particles); cudaFree(c->d_s);
+    c->d_particles = nullptr; c->d_s = nullptr;
+    c->n_particles = n;
+    c->alpha_min_build = alpha_min;
+    if (n == 0) return 0;
+    unsigned char* d_rows = nullptr;
+    CU(c, cudaMalloc(&d_rows, n * (size_t)row_stride));
+    cudaError_t e = cudaMalloc(&c->d_particles, n * 236ull);
+    if (e == cudaSuccess) e = cudaMalloc(&c->d_s, n * sizeof(float));
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_rows, host_rows, n * (size_t)row_stride, cudaMemcpyHostToDevice, c->own_stream);
+    int rc = 0;
+    if (e == cudaSuccess) rc = particles_activate(d_rows, L, (uint32_t)n, alpha_min, reinterpret_cast<float*>(c->d_particles), c->d_s, c->own_stream, &c->launches);
+    if (e == cudaSuccess && rc == 0) e = cudaStreamSynchronize(c->own_stream);
+    cudaFree(d_rows);
+    if (e != cudaSuccess || rc != 0) {
+        cudaFree(c->d_particles); cudaFree(c->d_s);
+        c->d_particles = nullptr; c->d_s = nullptr; c->n_particles = 0;
+        return fail(c, "grtSetParticlesRaw: %s", cudaGetErrorString(e != cudaSuccess ? e : (cudaError_t)rc));
+    }
+    return 0;
+}
+
+static int ply_type_size(const std::string& t) {
+    if (t == "char" || t == "uchar" || t == "int8" || t == "uint8") return 1;
+    if (t == "short" || t == "ushort" || t == "int16" || t == "uint16") return 2;
+    if (t == "int" || t == "uint" || t == "float" || t == "int32" || t == "uint32" || t == "float32") return 4;
+    if (t == "double" || t == "float64") return 8;
+    return 0;
+}
+
+// Own reader for the file layout GaussianData::parse accepts (src/GaussianData.cpp:25-95): binary little-endian, a "vertex"
+// element with the 59 named float properties in any order, extra properties ignored, missing ones are an error (happly.h:857).
+int grtLoadPly(grtContext* c, const char* path, float alpha_min, uint64_t* n_out, float* center3_out) {
+    if (!c) return 1;
+    if (!path) return fail(c, "grtLoadPly: path is NULL");
+    const int fd = open(path, O_RDONLY);
+    if (fd < 0) return fail(c, "grtLoadPly: cannot open %s", path);
+    struct stat st;
+    if (fstat(fd, &st) != 0 || st.st_size <= 0) { close(fd); return fail(c, "grtLoadPly: cannot stat %s", path); }
+    const size_t fsize = (size_t)st.st_size;
+    void* map = mmap(nullptr, fsize, PROT_READ, MAP_PRIVATE, fd, 0);
+    close(fd);
+    if (map == MAP_FAILED) return fail(c, "grtLoadPly: mmap of %s failed", path);
+    const char* f = static_cast<const char*>(map);
+    struct Unmap { void* p; size_t n; ~Unmap() { munmap(p, n); } } unmap{map, fsize};
+    // ---- header
+    size_t pos = 0;
+    auto next_line = [&](std::string& line) -> bool {
+        if (pos >= fsize) return false;
+        size_t e = pos;
+        while (e < fsize && f[e] != '\n') ++e;
+        if (e >= fsize) return false;
+        line.assign(f + pos, e - pos);
+        if (!line.empty() && line.back() == '\r') line.pop_back();
+        pos = e + 1;
+        return true;
+    };
+    std::string line;
+    if (!next_line(line) || line != "ply") return fail(c, "grtLoadPly: %s is not a PLY file", path);
+    bool fmt_ok = false, in_vertex = false, seen_vertex = false, done = false;
+    uint64_t n = 0, skip_before = 0, cur_count = 0;
+    uint32_t stride = 0, cur_stride = 0;
+    uint32_t off[59];
+    bool found[59] = {false};
+    while (next_line(line)) {
+        char a[64] = {0}, b[64] = {0}, d[64] = {0};
+        const int k = sscanf(line.c_str(), "%63s %63s %63s", a, b, d);
+        if (k <= 0) continue;
+        const std::string w = a;
+        if (w == "end_header") { done = true; break; }
+        if (w == "comment" || w == "obj_info") continue;
+        if (w == "format") {
+            if (std::string(b) != "binary_little_endian") return fail(c, "grtLoadPly: only binary_little_endian PLY is supported (got %s)", b);
+            fmt_ok = true;
+        } else if (w == "element") {
+            if (!seen_vertex) skip_before += cur_count * (uint64_t)cur_stride;
+            in_vertex = std::string(b) == "vertex";
+            cur_count = strtoull(d, nullptr, 10);
+            cur_stride = 0;
+            if (in_vertex) { seen_vertex = true; n = cur_count; }
+        } else if (w == "property") {
+            if (std::string(b) == "list") {
+                if (in_vertex || !seen_vertex) return fail(c, "grtLoadPly: list properties in or before the vertex element are not supported");
+                continue;
+            }
+            const int sz = ply_type_size(b);
+            if (!sz) return fail(c, "grtLoadPly: unknown property type %s", b);
+            if (in_vertex) {
+                for (int q = 0; q < 59; ++q)
+                    if (!found[q] && std::string(d) == kPlyProps[q]) {
+                        if (sz != 4 || !(std::string(b) == "float" || std::string(b) == "float32"))
+                            return fail(c, "grtLoadPly: property %s must be float", d);
+                        found[q] = true; off[q] = stride; break;
+                    }
+                stride += (uint32_t)sz;
+            } else {
+                cur_stride += (uint32_t)sz;
+            }
+        }
+    }
+    if (!done || !fmt_ok || !seen_vertex) return fail(c, "grtLoadPly: malformed header in %s", path);
+    for (int q = 0; q < 59; ++q)
+        if (!found[q]) return fail(c, "grtLoadPly: vertex property %s not found", kPlyProps[q]);  // happly.h:857 throws here
+    const size_t data0 = pos + (size_t)skip_before;
+    if (data0 + (size_t)n * stride > fsize) return fail(c, "grtLoadPly: %s is truncated (%llu vertices of %u bytes expected)", path, (unsigned long long)n, stride);
+    const unsigned char* rows = reinterpret_cast<const unsigned char*>(f) + data0;
+    int rc = grtSetParticlesRaw(c, rows, n, stride, off, alpha_min);
+    if (rc) return rc;
+    if (n_out) *n_out = n;
+    if (center3_out) {  // GaussianData::getCenter (src/GaussianData.cpp:140-152): sequential float sums in vertex order
+        float cx = 0.f, cy = 0.f, cz = 0.f;
+        for (uint64_t i = 0; i < n; ++i) {
+            float v[3];
+            memcpy(&v[0], rows + i * stride + off[0], 4); memcpy(&v[1], rows + i * stride + off[1], 4); memcpy(&v[2], rows + i * stride + off[2], 4);
+            cx += v[0]; cy += v[1]; cz += v[2];
+        }
+        const float fn = static_cast<float>(n);
+        center3_out[0] = cx / fn; center3_out[1] = cy / fn; center3_out[2] = cz / fn;
+    }
+    return 0;
+}
+
+int grtGetParticles(grtContext* c, void* host_out236, uint64_t n) {
+    if (!c) return 1;
+    if (n > c->n_particles) return fail(c, "grtGetParticles: %llu requested, %llu resident", (unsigned long long)n, (unsigned long long)c->n_particles);
+    if (n && !host_out236) return fail(c, "grtGetParticles: host buffer is NULL");
+    if (n) CU(c, cudaMemcpy(host_out236, c->d_particles, n * 236ull, cudaMemcpyDeviceToHost));
     return 0;
 }
 

@@ -104,6 +104,14 @@ int particles_compute_boxes(const void* d_particles236, const float* d_s, uint32
                             cudaStream_t stream, unsigned long long* launches);
 int particles_gather(const void* d_particles236, const float* d_s, const uint32_t* d_perm, uint32_t n_live, PRec* d_recs,
                      float4* d_sh, cudaStream_t stream, unsigned long long* launches);
+// raw PLY vertex rows -> records + proxy radii (ingest.cu).  off[k]: byte offset inside a row of the k-th of the 59 properties
+// x y z scale_0-2 rot_0-3 opacity f_dc_0-2 f_rest_0-44; aligned: stride and every offset are multiples of 4.
+struct PlyLayout {
+    uint32_t stride, aligned;
+    uint32_t off[59];
+};
+int particles_activate(const unsigned char* d_rows, const PlyLayout& L, uint32_t n, float alpha_min, float* d_out59, float* d_s,
+                       cudaStream_t stream, unsigned long long* launches);
 // triangle soup: d_tri9 = n x 9 floats (world-space v0,v1,v2), d_meta = n x (mesh, face)
 int mesh_compute_boxes(const float* d_tri9, uint32_t n_tris, float4* d_lo, float4* d_hi, cudaStream_t stream,
                        unsigned long long* launches);

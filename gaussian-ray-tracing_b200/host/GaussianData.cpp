@@ -48,6 +48,10 @@ GaussianData::GaussianData(const std::string& filename) : m_filename(filename) {
     printf("Loading PLY file: %s\n", filename.c_str());
     loadPly();
 }
+GaussianData::GaussianData(const std::string& filename, bool deferred) : m_filename(filename), m_deferred(deferred) {
+    printf("Loading PLY file: %s\n", filename.c_str());
+    if (!deferred) loadPly();
+}
 GaussianData::~GaussianData() {}
 
 namespace {
@@ -161,6 +165,7 @@ void GaussianData::loadPly() {
 }
 
 float3 GaussianData::getCenter() {  // src/GaussianData.cpp:140-152: sequential float sums
+    if (m_deferred) return m_center;  // computed the same way by grtLoadPly
     float3 c; c.x = c.y = c.z = 0.0f;
     for (auto& p : particles) { c.x += p.position[0]; c.y += p.position[1]; c.z += p.position[2]; }
     const float n = static_cast<float>(particles.size());

@@ -18,12 +18,21 @@ static_assert(sizeof(GaussianParticle) == 236, "GaussianParticle must stay 236 b
 class GaussianData {
 public:
     GaussianData(const std::string& filename);  // throws std::runtime_error on a missing file / property, like happly
+    // addition: deferred = true reads nothing on the host; GaussianTracer then ingests the file on the device
+    // (grtLoadPly: mmap + CUDA activation kernel) and reports count and centre back through setDeviceIngested().
+    GaussianData(const std::string& filename, bool deferred);
     ~GaussianData();
-    size_t getVertexCount() const { return particles.size(); }
+    size_t getVertexCount() const { return m_deferred ? m_count : particles.size(); }
     float3 getCenter();
-    std::vector<GaussianParticle> particles;
+    std::vector<GaussianParticle> particles;  // empty in deferred mode (the records live on the device: grtGetParticles)
+    bool deferred() const { return m_deferred; }
+    const std::string& filename() const { return m_filename; }
+    void setDeviceIngested(size_t count, float3 center) { m_count = count; m_center = center; }
 
 private:
     void loadPly();
     std::string m_filename;
+    bool m_deferred = false;
+    size_t m_count = 0;
+    float3 m_center{};
 };

@@ -5,13 +5,25 @@
 
 #include "Exception.h"
 
-GaussianTracer::GaussianTracer(const std::string& filename, int device) : m_gsData(filename) {
+GaussianTracer::GaussianTracer(const std::string& filename, int device, bool device_ingest) : m_gsData(filename, device_ingest) {
     stream = nullptr;
     memset(&params, 0, sizeof(params));
-    particle_count = m_gsData.getVertexCount();
     alpha_min = 0.01f;  // GaussianTracer.cpp:45
     current_lookat.x = current_lookat.y = current_lookat.z = 0.0f;
     if (grtCreate(device, &m_ctx) != 0) throw std::runtime_error(std::string("grtCreate failed: ") + grtGetLastError(nullptr));
+    if (device_ingest) {  // the constructor must leave count and centre valid (main.cpp:66 asks for the centre before init)
+        uint64_t n = 0;
+        float cen[3] = {0.f, 0.f, 0.f};
+        if (grtLoadPly(m_ctx, filename.c_str(), alpha_min, &n, cen) != 0) {
+            const std::string msg = grtGetLastError(m_ctx);
+            grtDestroy(m_ctx);
+            m_ctx = nullptr;
+            throw std::runtime_error(msg);
+        }
+        float3 c; c.x = cen[0]; c.y = cen[1]; c.z = cen[2];
+        m_gsData.setDeviceIngested((size_t)n, c);
+    }
+    particle_count = m_gsData.getVertexCount();
 }
 
 GaussianTracer::~GaussianTracer() {
@@ -29,7 +41,7 @@ void GaussianTracer::setSize(unsigned int width, unsigned int height) {
 
 // Replaces createContext .. createSBT + createGaussianParticlesBVH + initializeParams (GaussianTracer.cpp:72-83).
 void GaussianTracer::initializeOptix() {
-    GRT_CHECK(m_ctx, grtSetParticles(m_ctx, m_gsData.particles.data(), particle_count, alpha_min));
+    if (!m_gsData.deferred()) GRT_CHECK(m_ctx, grtSetParticles(m_ctx, m_gsData.particles.data(), particle_count, alpha_min));
     void* d_particles = nullptr;
     uint64_t handle = 0;
     GRT_CHECK(m_ctx, grtBuildParticleAccel(m_ctx, nullptr, &handle, &d_particles));

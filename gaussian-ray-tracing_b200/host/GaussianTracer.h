@@ -17,7 +17,8 @@ enum ReflectionPrimitiveType { PLANE = 0, SPHERE, CUSTOM };
 
 class GaussianTracer {
 public:
-    GaussianTracer(const std::string& filename, int device = 0);
+    // device_ingest (addition): the PLY is activated on the GPU (grtLoadPly) instead of by GaussianData on the host
+    GaussianTracer(const std::string& filename, int device = 0, bool device_ingest = false);
     ~GaussianTracer();
 
     void initializeOptix();

@@ -11,7 +11,7 @@
 int main(int argc, char** argv) {
     std::string ply = "../data/train.ply", out = "frame.ppm";
     unsigned width = 1280, height = 720, deg = 0, frames = 1;
-    bool fisheye = false, plane = false, sphere = false;
+    bool fisheye = false, plane = false, sphere = false, device_ingest = false;
     int type = MIRROR;
     for (int i = 1; i < argc; ++i) {
         auto next = [&](const char* flag) -> const char* {
@@ -28,13 +28,14 @@ int main(int argc, char** argv) {
         else if (!strcmp(argv[i], "--fisheye")) fisheye = true;
         else if (!strcmp(argv[i], "--plane")) plane = true;
         else if (!strcmp(argv[i], "--sphere")) sphere = true;
+        else if (!strcmp(argv[i], "--device-ingest")) device_ingest = true;
         else if (!strcmp(argv[i], "-h") || !strcmp(argv[i], "--help")) {
-            printf("usage: grt_render -p scene.ply [--width W --height H --sh-degree 0..3 --fisheye --plane --sphere --type 0|1|2 --frames N --out frame.ppm]\n");
+            printf("usage: grt_render -p scene.ply [--width W --height H --sh-degree 0..3 --fisheye --plane --sphere --device-ingest --type 0|1|2 --frames N --out frame.ppm]\n");
             return 0;
         } else { fprintf(stderr, "unknown flag %s\n", argv[i]); return 2; }
     }
     try {
-        GaussianTracer tracer(ply);
+        GaussianTracer tracer(ply, 0, device_ingest);
         tracer.setSize(width, height);
         tracer.initializeOptix();
         CUDAOutputBuffer output_buffer(tracer.context(), (int32_t)width, (int32_t)height);

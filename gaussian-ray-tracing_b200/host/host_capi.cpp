@@ -56,11 +56,11 @@ int grtHostPrimitive(int kind, const float pos[3], unsigned* n_vertices, unsigne
 }
 
 // The reference's start-up + one frame (src/main.cpp:62-100) through the C++ facade; rgb8_out = width*height*3 bytes.
-// flags: bit0 fisheye, bit1 createPlane, bit2 createSphere.  Returns 0, or 1 with the message in err (if given).
+// flags: bit0 fisheye, bit1 createPlane, bit2 createSphere, bit3 device-side PLY ingest.  Returns 0, or 1 with the message in err (if given).
 int grtHostRenderPly(const char* ply, unsigned width, unsigned height, unsigned sh_degree, unsigned flags, int mesh_type,
                      unsigned char* rgb8_out, float* kernel_ms_out, char* err, unsigned err_len) {
     try {
-        GaussianTracer tracer{std::string(ply)};
+        GaussianTracer tracer{std::string(ply), 0, (flags & 8u) != 0};
         tracer.setSize(width, height);
         tracer.initializeOptix();
         CUDAOutputBuffer out(tracer.context(), (int32_t)width, (int32_t)height);

@@ -104,6 +104,19 @@ const char* grtGetLastError(const grtContext* ctx); /* ctx may be NULL: error of
  * alpha_min sizes the proxies: s = sqrt(2 ln(opacity/alpha_min)) (src/GaussianTracer.cpp:306). */
 int grtSetParticles(grtContext* ctx, const void* host_particles, uint64_t n, float alpha_min);
 
+/* Device-side ingest (replaces the activation loop of GaussianData::parse, src/GaussianData.cpp:97-131, and the proxy-size
+ * loop of src/GaussianTracer.cpp:304-306): host_rows = n raw PLY vertex rows of row_stride bytes as they lie in the file,
+ * prop_offsets59[k] = byte offset inside a row of the k-th of the float properties x y z scale_0-2 rot_0-3 opacity
+ * f_dc_0-2 f_rest_0-44.  exp / sigmoid / quaternion normalisation / SH re-ordering run in one CUDA kernel; the resident
+ * result is the same 236-byte record array grtSetParticles would have uploaded. */
+int grtSetParticlesRaw(grtContext* ctx, const void* host_rows, uint64_t n, uint32_t row_stride, const uint32_t* prop_offsets59, float alpha_min);
+/* GaussianData::GaussianData(path) + parse (src/GaussianData.cpp:8-132) in one call: own binary-LE reader (mmap, no
+ * column copies), then grtSetParticlesRaw.  center3_out = GaussianData::getCenter (:140-152).  Errors like the
+ * reference: unreadable file, missing property (happly.h:857). */
+int grtLoadPly(grtContext* ctx, const char* path, float alpha_min, uint64_t* n_out, float* center3_out);
+/* GaussianData::getParticles equivalent: downloads the first n resident 236-byte records. */
+int grtGetParticles(grtContext* ctx, void* host_out236, uint64_t n);
+
 /* replaces createGaussianParticlesBVH: createGAS + N x createIAS + optixAccelBuild
  * (src/GaussianTracer.cpp:297-317, 379, 401-473).  LBVH on the device.  handle_out -> Params.handle,
  * d_particles_out -> Params.d_particles. */
