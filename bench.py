@@ -219,7 +219,7 @@ def main():
         k_ms = float(np.mean(kernel_ms))
         achieved = rays * bytes_per_ray / (k_ms * 1e-3) / 1e9
         traffic = None  # dram__bytes_read.sum + dram__bytes_write.sum of trace_kernel from the committed ncu capture
-        ncu_path = os.path.join(ROOT, "profiles", "r1_trace_kernel_ncu.json")
+        ncu_path = os.path.join(ROOT, "profiles", "r1_v9_trace_kernel_ncu.json")
         if os.path.exists(ncu_path) and not args.fisheye:
             traffic = json.load(open(ncu_path)).get("dram_bytes_per_launch")
         line = {
@@ -238,7 +238,7 @@ def main():
             "clocks": sampler.result(),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                          "algorithmic_bytes_per_launch": rays * bytes_per_ray,
-                         "peak_source": peak_src, "algorithmic_bytes_per_ray": bytes_per_ray, "kernel": "trace_kernel<false>"},
+                         "peak_source": peak_src, "algorithmic_bytes_per_ray": bytes_per_ray, "kernel": "trace_kernel<false,false> (STATS off, no-mesh specialisation)"},
         }
         if world == 1 and not args.no_cpu_baseline:
             from oracle import orc  # checker / baseline only
