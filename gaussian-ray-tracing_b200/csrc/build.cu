@@ -110,13 +110,39 @@ __global__ void __launch_bounds__(RS_THREADS) rs_scatter_kernel(const uint64_t* 
     }
 }
 
+void BuildScratch::begin() {
+    if (want > cap) {
+        if (base) cudaFree(base);
+        base = nullptr;
+        cap = 0;
+        const size_t ask = want + want / 8 + (1u << 20);
+        if (cudaMalloc(&base, ask) == cudaSuccess) cap = ask; else { base = nullptr; (void)cudaGetLastError(); }
+    }
+    off = 0;
+    want = 0;
+}
+void* BuildScratch::get(size_t bytes) {
+    bytes = (bytes + 255) & ~(size_t)255;
+    want += bytes;
+    if (off + bytes > cap) return nullptr;
+    void* p = base + off;
+    off += bytes;
+    return p;
+}
+void BuildScratch::release() {
+    if (base) cudaFree(base);
+    base = nullptr;
+    cap = off = want = 0;
+}
+
 int radix_sort_pairs(uint64_t* d_keys, uint64_t* d_keys_tmp, uint32_t* d_vals, uint32_t* d_vals_tmp, uint32_t n,
-                     cudaStream_t stream, unsigned long long* launches, bool* result_in_tmp) {
+                     cudaStream_t stream, unsigned long long* launches, bool* result_in_tmp, BuildScratch* scratch) {
     *result_in_tmp = false;
     if (n == 0) return 0;
     const uint32_t nblocks = cdiv(n, RS_TILE);
-    uint32_t* d_hist = nullptr;
-    CK(cudaMalloc(&d_hist, sizeof(uint32_t) * 256ull * nblocks));
+    uint32_t* d_hist = scratch ? static_cast<uint32_t*>(scratch->get(sizeof(uint32_t) * 256ull * nblocks)) : nullptr;
+    const bool own_hist = d_hist == nullptr;
+    if (own_hist) CK(cudaMalloc(&d_hist, sizeof(uint32_t) * 256ull * nblocks));
     uint64_t* kin = d_keys; uint64_t* kout = d_keys_tmp;
     uint32_t* vin = d_vals; uint32_t* vout = d_vals_tmp;
     for (int pass = 0; pass < 8; ++pass) {
@@ -129,9 +155,11 @@ int radix_sort_pairs(uint64_t* d_keys, uint64_t* d_keys_tmp, uint32_t* d_vals, u
         std::swap(vin, vout);
     }
     // 8 passes: the result is back in the original buffers
-    cudaError_t e = cudaStreamSynchronize(stream);
-    cudaFree(d_hist);
-    if (e != cudaSuccess) return (int)e;
+    if (own_hist) {
+        cudaError_t e = cudaStreamSynchronize(stream);
+        cudaFree(d_hist);
+        if (e != cudaSuccess) return (int)e;
+    }
     CK(cudaGetLastError());
     return 0;
 }
@@ -374,19 +402,30 @@ __global__ void tiny_root_kernel(const float4* __restrict__ lo, const float4* __
         write_child(&nodes[0], k, make_float4(INFINITY, INFINITY, INFINITY, 0.f), make_float4(-INFINITY, -INFINITY, -INFINITY, 0.f), CHILD_EMPTY);
 }
 
-struct DevBuf {  // frees on scope exit
+struct DevBuf {  // a build temporary: from the context's scratch block, else cudaMalloc'd and freed on scope exit
     void* p = nullptr;
-    ~DevBuf() { if (p) cudaFree(p); }
-    cudaError_t alloc(size_t bytes) { return cudaMalloc(&p, bytes ? bytes : 1); }
+    bool owned = false;
+    BuildScratch* scratch = nullptr;
+    ~DevBuf() { if (p && owned) cudaFree(p); }
+    cudaError_t alloc(size_t bytes) {
+        p = scratch ? scratch->get(bytes ? bytes : 1) : nullptr;
+        if (p) return cudaSuccess;
+        owned = true;
+        return cudaMalloc(&p, bytes ? bytes : 1);
+    }
     template <class T> T* as() { return reinterpret_cast<T*>(p); }
 };
 
-int lbvh_build(const float4* d_lo, const float4* d_hi, uint32_t n, cudaStream_t stream, LbvhResult* out, unsigned long long* launches) {
+int lbvh_build(const float4* d_lo, const float4* d_hi, uint32_t n, cudaStream_t stream, LbvhResult* out, unsigned long long* launches,
+               BuildScratch* scratch) {
+    WideNode* const reuse_nodes = out->reuse_nodes;
+    const uint32_t reuse_cap = out->reuse_cap;
     *out = LbvhResult();
     if (n == 0) return 0;
     if (n >= (1u << 28)) return (int)cudaErrorInvalidValue;
     const int TB = 256;
     DevBuf bounds, keys, keys2, vals2;
+    bounds.scratch = keys.scratch = keys2.scratch = vals2.scratch = scratch;
     CK(bounds.alloc(8 * sizeof(uint32_t)));
     const uint32_t h_init[8] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u, 0u, 0u, 0u};
     CK(cudaMemcpyAsync(bounds.p, h_init, sizeof(h_init), cudaMemcpyHostToDevice, stream));
@@ -395,13 +434,14 @@ int lbvh_build(const float4* d_lo, const float4* d_hi, uint32_t n, cudaStream_t 
     CK(keys.alloc(sizeof(uint64_t) * n));
     CK(keys2.alloc(sizeof(uint64_t) * n));
     CK(vals2.alloc(sizeof(uint32_t) * n));
-    uint32_t* d_perm = nullptr;
-    CK(cudaMalloc(&d_perm, sizeof(uint32_t) * n));
+    uint32_t* d_perm = scratch ? static_cast<uint32_t*>(scratch->get(sizeof(uint32_t) * n)) : nullptr;
+    out->perm_owned = d_perm == nullptr;
+    if (!d_perm) CK(cudaMalloc(&d_perm, sizeof(uint32_t) * n));
     out->perm = d_perm;
     morton_kernel<<<cdiv(n, TB), TB, 0, stream>>>(d_lo, d_hi, n, bounds.as<uint32_t>(), keys.as<uint64_t>(), d_perm);
     ++*launches;
     bool in_tmp = false;
-    int rc = radix_sort_pairs(keys.as<uint64_t>(), keys2.as<uint64_t>(), d_perm, vals2.as<uint32_t>(), n, stream, launches, &in_tmp);
+    int rc = radix_sort_pairs(keys.as<uint64_t>(), keys2.as<uint64_t>(), d_perm, vals2.as<uint32_t>(), n, stream, launches, &in_tmp, scratch);
     if (rc) return rc;
     uint32_t h_bounds[8];
     CK(cudaMemcpyAsync(h_bounds, bounds.p, sizeof(h_bounds), cudaMemcpyDeviceToHost, stream));
@@ -412,8 +452,8 @@ int lbvh_build(const float4* d_lo, const float4* d_hi, uint32_t n, cudaStream_t 
     if (nl == 0) return 0;
 
     if (nl <= (uint32_t)LEAF_MAX) {
-        WideNode* nodes = nullptr;
-        CK(cudaMalloc(&nodes, sizeof(WideNode)));
+        WideNode* nodes = reuse_cap >= 1 ? reuse_nodes : nullptr;
+        if (!nodes) CK(cudaMalloc(&nodes, sizeof(WideNode)));
         tiny_root_kernel<<<1, 32, 0, stream>>>(d_lo, d_hi, d_perm, nl, nodes);
         ++*launches;
         CK(cudaStreamSynchronize(stream));
@@ -424,6 +464,7 @@ int lbvh_build(const float4* d_lo, const float4* d_hi, uint32_t n, cudaStream_t 
     }
 
     DevBuf left, right, parent, first, last, blo, bhi, flags, qa, qb, ctr, wide_tmp;
+    for (DevBuf* b : {&left, &right, &parent, &first, &last, &blo, &bhi, &flags, &qa, &qb, &ctr, &wide_tmp}) b->scratch = scratch;
     CK(left.alloc(4ull * (nl - 1)));
     CK(right.alloc(4ull * (nl - 1)));
     CK(first.alloc(4ull * (nl - 1)));
@@ -469,8 +510,8 @@ int lbvh_build(const float4* d_lo, const float4* d_hi, uint32_t n, cudaStream_t 
     }
     CK(cudaGetLastError());
     const uint32_t n_nodes = h_ctr[0];
-    WideNode* nodes = nullptr;
-    CK(cudaMalloc(&nodes, sizeof(WideNode) * (size_t)n_nodes));
+    WideNode* nodes = n_nodes <= reuse_cap ? reuse_nodes : nullptr;
+    if (!nodes) CK(cudaMalloc(&nodes, sizeof(WideNode) * (size_t)n_nodes));
     CK(cudaMemcpyAsync(nodes, wide_tmp.p, sizeof(WideNode) * (size_t)n_nodes, cudaMemcpyDeviceToDevice, stream));
     CK(cudaStreamSynchronize(stream));
     out->nodes = nodes;

@@ -39,6 +39,9 @@ struct grtContext {
     float4* p_sh = nullptr;
     AccelHeader* d_p_header = nullptr;
     uint32_t p_live = 0, p_nnodes = 0, p_levels = 0;
+    uint32_t p_nodes_cap = 0, p_recs_cap = 0;  // capacities of p_nodes / p_recs+p_sh: rebuilds reuse the arrays
+    uint64_t particles_cap = 0;                // capacity (records) of d_particles / d_s
+    bool p_valid = false;                      // the particle accel matches the resident particle set
     // meshes
     std::vector<float> h_tri9;
     std::vector<uint2> h_meta;
@@ -58,11 +61,13 @@ struct grtContext {
     bool counters_on = false;
     DeviceCounters* d_counters = nullptr;
     uint32_t* d_tile_counter = nullptr;
+    BuildScratch scratch;  // builder temporaries, kept between builds
     int sm_count = 0;
     // e2e frame
     uint8_t* d_frame = nullptr;
     size_t frame_bytes = 0;
     cudaStream_t own_stream = nullptr;
+    cudaEvent_t ev_b0 = nullptr, ev_b1 = nullptr;  // build timing
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool ev_valid = false;
     grtBuildInfo info{};
@@ -94,6 +99,19 @@ static void free_particle_accel(grtContext* c) {
     cudaFree(c->p_nodes); cudaFree(c->p_recs); cudaFree(c->p_sh); cudaFree(c->d_p_header);
     c->p_nodes = nullptr; c->p_recs = nullptr; c->p_sh = nullptr; c->d_p_header = nullptr;
     c->p_live = c->p_nnodes = c->p_levels = 0;
+    c->p_nodes_cap = c->p_recs_cap = 0;
+    c->p_valid = false;
+}
+// d_particles / d_s hold at least n records (kept when large enough: per-frame particle updates do not reallocate)
+static int reserve_particles(grtContext* c, uint64_t n) {
+    if (n <= c->particles_cap && c->d_particles && c->d_s) return 0;
+    cudaFree(c->d_particles); cudaFree(c->d_s);
+    c->d_particles = nullptr; c->d_s = nullptr; c->particles_cap = 0;
+    cudaError_t e = cudaMalloc(&c->d_particles, n * 236ull);
+    if (e == cudaSuccess) e = cudaMalloc(&c->d_s, n * sizeof(float));
+    if (e != cudaSuccess) return (int)e;
+    c->particles_cap = n;
+    return 0;
 }
 static void free_mesh_accel(grtContext* c) {
     cudaFree(c->m_nodes); cudaFree(c->m_tris); cudaFree(c->d_m_header); cudaFree(c->d_meshes);
@@ -136,7 +154,10 @@ int grtDestroy(grtContext* c) {
     free_particle_accel(c);
     free_mesh_accel(c);
     cudaFree(c->d_particles); cudaFree(c->d_s); cudaFree(c->d_counters); cudaFree(c->d_tile_counter); cudaFree(c->d_frame);
+    c->scratch.release();
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    if (c->ev_b0) cudaEventDestroy(c->ev_b0);
+    if (c->ev_b1) cudaEventDestroy(c->ev_b1);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     delete c;
@@ -192,9 +213,7 @@ int grtSetParticles(grtContext* c, const void* host_particles, uint64_t n, float
     if (n && !host_particles) return fail(c, "grtSetParticles: host_particles is NULL");
     if (n >= (1ull << 28)) return fail(c, "grtSetParticles: %llu particles exceed the 2^28 limit", (unsigned long long)n);
     CU(c, cudaSetDevice(c->device));
-    free_particle_accel(c);
-    cudaFree(c->d_particles); cudaFree(c->d_s);
-    c->d_particles = nullptr; c->d_s = nullptr;
+    c->p_valid = false;  // the accel (if any) belongs to the previous particle set; its arrays are reused by the next build
     c->n_particles = n;
     c->alpha_min_build = alpha_min;
     if (n == 0) return 0;
@@ -212,8 +231,7 @@ int grtSetParticles(grtContext* c, const void* host_particles, uint64_t n, float
         }
         s[i] = v;
     }
-    CU(c, cudaMalloc(&c->d_particles, n * 236ull));
-    CU(c, cudaMalloc(&c->d_s, n * sizeof(float)));
+    RC(c, reserve_particles(c, n));
     CU(c, cudaMemcpy(c->d_particles, host_particles, n * 236ull, cudaMemcpyHostToDevice));
     CU(c, cudaMemcpy(c->d_s, s.data(), n * sizeof(float), cudaMemcpyHostToDevice));
     return 0;
@@ -242,24 +260,20 @@ int grtSetParticlesRaw(grtContext* c, const void* host_rows, uint64_t n, uint32_
         if (off59[k] & 3u) L.aligned = 0;
     }
     CU(c, cudaSetDevice(c->device));
-    free_particle_accel(c);
-    cudaFree(c->d_particles); cudaFree(c->d_s);
-    c->d_particles = nullptr; c->d_s = nullptr;
+    c->p_valid = false;
     c->n_particles = n;
     c->alpha_min_build = alpha_min;
     if (n == 0) return 0;
     unsigned char* d_rows = nullptr;
     CU(c, cudaMalloc(&d_rows, n * (size_t)row_stride));
-    cudaError_t e = cudaMalloc(&c->d_particles, n * 236ull);
-    if (e == cudaSuccess) e = cudaMalloc(&c->d_s, n * sizeof(float));
+    cudaError_t e = (cudaError_t)reserve_particles(c, n);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_rows, host_rows, n * (size_t)row_stride, cudaMemcpyHostToDevice, c->own_stream);
     int rc = 0;
     if (e == cudaSuccess) rc = particles_activate(d_rows, L, (uint32_t)n, alpha_min, reinterpret_cast<float*>(c->d_particles), c->d_s, c->own_stream, &c->launches);
     if (e == cudaSuccess && rc == 0) e = cudaStreamSynchronize(c->own_stream);
     cudaFree(d_rows);
     if (e != cudaSuccess || rc != 0) {
-        cudaFree(c->d_particles); cudaFree(c->d_s);
-        c->d_particles = nullptr; c->d_s = nullptr; c->n_particles = 0;
+        c->n_particles = 0;
         return fail(c, "grtSetParticlesRaw: %s", cudaGetErrorString(e != cudaSuccess ? e : (cudaError_t)rc));
     }
     return 0;
@@ -377,45 +391,66 @@ int grtBuildParticleAccel(grtContext* c, void* stream_v, uint64_t* handle_out, v
     if (!c) return 1;
     cudaStream_t stream = (cudaStream_t)stream_v;
     CU(c, cudaSetDevice(c->device));
-    free_particle_accel(c);
+    // A rebuild (dynamic particle sets: grtSetParticles* + grtBuildParticleAccel per frame) keeps the node / record / SH
+    // arrays of the previous accel when they are large enough and takes its temporaries from the context's scratch block.
+    c->p_valid = false;
+    c->p_live = c->p_nnodes = c->p_levels = 0;
     if (handle_out) *handle_out = 0;
     if (d_particles_out) *d_particles_out = c->d_particles;
     c->info.n_particles = c->n_particles;
     c->info.n_live = 0; c->info.n_wide_nodes = 0; c->info.wide_depth_levels = 0; c->info.build_ms = 0;
     if (c->n_particles == 0) return 0;
     const uint32_t n = (uint32_t)c->n_particles;
-    cudaEvent_t e0, e1;
-    CU(c, cudaEventCreate(&e0));
-    CU(c, cudaEventCreate(&e1));
-    CU(c, cudaEventRecord(e0, stream));
-    float4 *d_lo = nullptr, *d_hi = nullptr;
-    CU(c, cudaMalloc(&d_lo, sizeof(float4) * (size_t)n));
-    CU(c, cudaMalloc(&d_hi, sizeof(float4) * (size_t)n));
+    if (!c->ev_b0) { CU(c, cudaEventCreate(&c->ev_b0)); CU(c, cudaEventCreate(&c->ev_b1)); }
+    CU(c, cudaEventRecord(c->ev_b0, stream));
+    c->scratch.begin();
+    float4* d_lo = static_cast<float4*>(c->scratch.get(sizeof(float4) * (size_t)n));
+    float4* d_hi = static_cast<float4*>(c->scratch.get(sizeof(float4) * (size_t)n));
+    const bool own_lo = !d_lo, own_hi = !d_hi;
+    if (own_lo) CU(c, cudaMalloc(&d_lo, sizeof(float4) * (size_t)n));
+    if (own_hi) CU(c, cudaMalloc(&d_hi, sizeof(float4) * (size_t)n));
     int rc = particles_compute_boxes(c->d_particles, c->d_s, n, d_lo, d_hi, stream, &c->launches);
     LbvhResult res;
-    if (!rc) rc = lbvh_build(d_lo, d_hi, n, stream, &res, &c->launches);
-    cudaFree(d_lo); cudaFree(d_hi);
-    if (rc) { cudaFree(res.perm); cudaFree(res.nodes); return fail(c, "particle accel build failed: %s", cudaGetErrorString((cudaError_t)rc)); }
-    c->p_live = res.n_live; c->p_nnodes = res.n_nodes; c->p_levels = res.levels; c->p_nodes = res.nodes;
+    res.reuse_nodes = c->p_nodes;
+    res.reuse_cap = c->p_nodes_cap;
+    if (!rc) rc = lbvh_build(d_lo, d_hi, n, stream, &res, &c->launches, &c->scratch);
+    if (own_lo) cudaFree(d_lo);
+    if (own_hi) cudaFree(d_hi);
+    if (rc) {
+        if (res.perm_owned) cudaFree(res.perm);
+        if (res.nodes != c->p_nodes) cudaFree(res.nodes);
+        return fail(c, "particle accel build failed: %s", cudaGetErrorString((cudaError_t)rc));
+    }
+    if (res.nodes && res.nodes != c->p_nodes) {
+        cudaFree(c->p_nodes);
+        c->p_nodes = res.nodes;
+        c->p_nodes_cap = res.n_nodes;
+    }
+    c->p_live = res.n_live; c->p_nnodes = res.n_nodes; c->p_levels = res.levels;
     if (res.n_live) {
-        CU(c, cudaMalloc(&c->p_recs, sizeof(PRec) * (size_t)res.n_live));
-        CU(c, cudaMalloc(&c->p_sh, sizeof(float4) * SH_F4 * (size_t)res.n_live));
+        if (res.n_live > c->p_recs_cap) {
+            cudaFree(c->p_recs); cudaFree(c->p_sh);
+            c->p_recs = nullptr; c->p_sh = nullptr; c->p_recs_cap = 0;
+            CU(c, cudaMalloc(&c->p_recs, sizeof(PRec) * (size_t)res.n_live));
+            CU(c, cudaMalloc(&c->p_sh, sizeof(float4) * SH_F4 * (size_t)res.n_live));
+            c->p_recs_cap = res.n_live;
+        }
         RC(c, particles_gather(c->d_particles, c->d_s, res.perm, res.n_live, c->p_recs, c->p_sh, stream, &c->launches));
         AccelHeader h{};
         h.magic = ACCEL_MAGIC_PARTICLES; h.nodes = c->p_nodes; h.recs = c->p_recs; h.sh = c->p_sh; h.tris = nullptr;
         h.n_prims = res.n_live; h.n_nodes = res.n_nodes;
-        CU(c, cudaMalloc(&c->d_p_header, sizeof(AccelHeader)));
+        if (!c->d_p_header) CU(c, cudaMalloc(&c->d_p_header, sizeof(AccelHeader)));
         CU(c, cudaMemcpyAsync(c->d_p_header, &h, sizeof(h), cudaMemcpyHostToDevice, stream));
+        c->p_valid = true;
     }
-    CU(c, cudaEventRecord(e1, stream));
+    CU(c, cudaEventRecord(c->ev_b1, stream));
     CU(c, cudaStreamSynchronize(stream));
-    cudaFree(res.perm);
+    if (res.perm_owned) cudaFree(res.perm);
     float ms = 0;
-    cudaEventElapsedTime(&ms, e0, e1);
-    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaEventElapsedTime(&ms, c->ev_b0, c->ev_b1);
     c->info.n_live = res.n_live; c->info.n_wide_nodes = res.n_nodes; c->info.wide_depth_levels = res.levels; c->info.build_ms = ms;
     for (int k = 0; k < 3; ++k) { c->info.scene_lo[k] = res.lo[k]; c->info.scene_hi[k] = res.hi[k]; }
-    if (handle_out) *handle_out = (uint64_t)(uintptr_t)c->d_p_header;  // 0 when nothing is live
+    if (handle_out) *handle_out = c->p_valid ? (uint64_t)(uintptr_t)c->d_p_header : 0;  // 0 when nothing is live
     return 0;
 }
 
@@ -500,13 +535,15 @@ int grtBuildMeshAccel(grtContext* c, void* stream_v, uint64_t* mesh_handle_out, 
     CU(c, cudaMemcpyAsync(d_meta, c->h_meta.data(), sizeof(uint2) * (size_t)nt, cudaMemcpyHostToDevice, stream));
     int rc = mesh_compute_boxes(d_tri9, nt, d_lo, d_hi, stream, &c->launches);
     LbvhResult res;
-    if (!rc) rc = lbvh_build(d_lo, d_hi, nt, stream, &res, &c->launches);
+    c->scratch.begin();
+    if (!rc) rc = lbvh_build(d_lo, d_hi, nt, stream, &res, &c->launches, &c->scratch);
     if (!rc && res.n_live) {
         rc = (int)cudaMalloc(&c->m_tris, sizeof(TriRec) * (size_t)res.n_live);
         if (!rc) rc = mesh_gather(d_tri9, d_meta, res.perm, res.n_live, c->m_tris, stream, &c->launches);
     }
     cudaError_t es = cudaStreamSynchronize(stream);
-    cudaFree(d_tri9); cudaFree(d_meta); cudaFree(d_lo); cudaFree(d_hi); cudaFree(res.perm);
+    cudaFree(d_tri9); cudaFree(d_meta); cudaFree(d_lo); cudaFree(d_hi);
+    if (res.perm_owned) cudaFree(res.perm);
     if (rc || es != cudaSuccess) { cudaFree(res.nodes); return fail(c, "mesh accel build failed: %s", cudaGetErrorString(rc ? (cudaError_t)rc : es)); }
     c->m_nodes = res.nodes; c->m_count = res.n_live; c->m_nnodes = res.n_nodes;
     if (res.n_live) {
@@ -533,7 +570,8 @@ static int do_launch(grtContext* c, cudaStream_t stream, const grtParams* p, uin
     if (p->sh_degree_max > 3) return fail(c, "grtLaunch: sh_degree_max %u > 3", p->sh_degree_max);
     // Handles are opaque device pointers owned by this context; anything else is a caller bug
     // (the reference would hand a stale OptixTraversableHandle to optixLaunch and crash).
-    if (p->handle != 0 && p->handle != (uint64_t)(uintptr_t)c->d_p_header) return fail(c, "grtLaunch: Params.handle is not this context's particle accel");
+    if (p->handle != 0 && (p->handle != (uint64_t)(uintptr_t)c->d_p_header || !c->p_valid))
+        return fail(c, "grtLaunch: Params.handle is not this context's (current) particle accel");
     if (p->mesh_handle != 0 && p->mesh_handle != (uint64_t)(uintptr_t)c->d_m_header) return fail(c, "grtLaunch: Params.mesh_handle is not this context's mesh accel");
     if (p->mesh_handle != 0 && p->d_meshes != (void*)c->d_meshes) return fail(c, "grtLaunch: Params.d_meshes does not belong to Params.mesh_handle");
     if (!p->output_buffer && !c->dbg_rgb32f) return fail(c, "grtLaunch: Params.output_buffer is NULL");

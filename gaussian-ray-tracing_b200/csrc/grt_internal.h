@@ -83,11 +83,23 @@ struct LaunchExtras {
 };
 
 // ---- generic LBVH builder (build.cu) ----
-struct BuildScratch;
+// Scratch arena of a context: the builder's ~20 temporaries are bump-allocated from one device block that is kept between
+// builds (cudaMalloc/cudaFree cost more than the build kernels: 13 ms -> ~3 ms per 1M-particle rebuild).  A build that
+// needs more than the block holds falls back to cudaMalloc for the overflow and the block grows before the next build.
+struct BuildScratch {
+    char* base = nullptr;
+    size_t cap = 0, off = 0, want = 0;
+    void begin();                 // start of a build: grow to what the last build asked for, rewind
+    void* get(size_t bytes);      // nullptr when the block is exhausted (caller cudaMallocs)
+    void release();               // free the block
+};
 struct LbvhResult {
-    WideNode* nodes = nullptr;  // cudaMalloc'd, exact size
+    WideNode* nodes = nullptr;  // cudaMalloc'd (exact size), or reuse_nodes when the tree fits into it
     uint32_t n_nodes = 0;
-    uint32_t* perm = nullptr;   // sorted position -> input index, n_live entries valid (cudaMalloc'd, n entries)
+    uint32_t* perm = nullptr;   // sorted position -> input index, n_live entries valid (n entries; scratch unless perm_owned)
+    bool perm_owned = true;     // perm was cudaMalloc'd: the caller frees it
+    WideNode* reuse_nodes = nullptr;  // in: a node array of an earlier build the caller is willing to overwrite
+    uint32_t reuse_cap = 0;           // in: its capacity in nodes
     uint32_t n_live = 0;
     uint32_t levels = 0;
     float lo[3], hi[3];
@@ -95,9 +107,9 @@ struct LbvhResult {
 // d_lo/d_hi: n boxes (float4, w ignored); dead boxes must have lo.x > hi.x (they sort last and are dropped).
 // Returns cudaError_t as int; launches counted into *launches.
 int lbvh_build(const float4* d_lo, const float4* d_hi, uint32_t n, cudaStream_t stream, LbvhResult* out,
-               unsigned long long* launches);
+               unsigned long long* launches, BuildScratch* scratch = nullptr);
 int radix_sort_pairs(uint64_t* d_keys, uint64_t* d_keys_tmp, uint32_t* d_vals, uint32_t* d_vals_tmp, uint32_t n,
-                     cudaStream_t stream, unsigned long long* launches, bool* result_in_tmp);
+                     cudaStream_t stream, unsigned long long* launches, bool* result_in_tmp, BuildScratch* scratch = nullptr);
 
 // particle pack kernels (build.cu)
 int particles_compute_boxes(const void* d_particles236, const float* d_s, uint32_t n, float4* d_lo, float4* d_hi,
