@@ -59,6 +59,8 @@ def main():
         if mirrors:
             ctx.set_meshes([]); ctx.build_mesh_accel()
     ctx.free(d_out)
+    if os.environ.get("GRT_SKIP_CONFIG4"):
+        return
     # configs[4]: 6M Gaussians, 3840x2160, 64-camera ring (all 64 on this one GPU; bench.py --gpus N partitions them)
     W, H = 3840, 2160
     rec = grt.activate(grt.synth_ply_properties(6_000_000, 1003))
