@@ -21,6 +21,7 @@ public:
     unsigned int getPBO() { return 0u; }
     const std::vector<uchar3>& download();            // synchronous device -> host copy
     void writePPM(const char* path);                  // binary P6, row 0 first (launch y = 0)
+    void writePNG(const char* path);                  // 8-bit RGB PNG (stored deflate blocks, no external library)
 
 private:
     grtContext* m_ctx;

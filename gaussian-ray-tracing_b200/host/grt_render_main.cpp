@@ -30,7 +30,7 @@ int main(int argc, char** argv) {
         else if (!strcmp(argv[i], "--sphere")) sphere = true;
         else if (!strcmp(argv[i], "--device-ingest")) device_ingest = true;
         else if (!strcmp(argv[i], "-h") || !strcmp(argv[i], "--help")) {
-            printf("usage: grt_render -p scene.ply [--width W --height H --sh-degree 0..3 --fisheye --plane --sphere --device-ingest --type 0|1|2 --frames N --out frame.ppm]\n");
+            printf("usage: grt_render -p scene.ply [--width W --height H --sh-degree 0..3 --fisheye --plane --sphere --device-ingest --type 0|1|2 --frames N --out frame.ppm|frame.png]\n");
             return 0;
         } else { fprintf(stderr, "unknown flag %s\n", argv[i]); return 2; }
     }
@@ -62,7 +62,8 @@ int main(int argc, char** argv) {
         }
         printf("rendered %u frame(s) %ux%u: %.3f ms/frame wall, last kernel %.3f ms\n", frames, width, height, total_ms / frames,
                tracer.lastKernelMs());
-        output_buffer.writePPM(out.c_str());
+        if (out.size() > 4 && out.substr(out.size() - 4) == ".png") output_buffer.writePNG(out.c_str());
+        else output_buffer.writePPM(out.c_str());
         printf("wrote %s\n", out.c_str());
     } catch (const std::exception& e) {
         fprintf(stderr, "error: %s\n", e.what());

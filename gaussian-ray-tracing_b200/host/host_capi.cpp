@@ -80,6 +80,10 @@ int grtHostRenderPly(const char* ply, unsigned width, unsigned height, unsigned 
         const std::vector<uchar3>& px = out.download();
         memcpy(rgb8_out, px.data(), px.size() * sizeof(uchar3));
         if (kernel_ms_out) *kernel_ms_out = tracer.lastKernelMs();
+        if (const char* sink = getenv("GRT_HOST_FRAME_SINK")) {  // test hook: also write the frame (".png" or PPM)
+            const std::string sp(sink);
+            if (sp.size() > 4 && sp.substr(sp.size() - 4) == ".png") out.writePNG(sink); else out.writePPM(sink);
+        }
         return 0;
     } catch (const std::exception& e) {
         if (err && err_len) { strncpy(err, e.what(), err_len - 1); err[err_len - 1] = 0; }

@@ -139,3 +139,50 @@ def test_cpp_facade_renders_like_python_facade(host, grt, ctx, tmp_path, flags, 
     # same kernels, same records; only libm-vs-numpy ulp differences in the host-side setup can differ
     assert (d > 1).mean() < 0.002 and out.max() > 0, (d.max(), (d > 0).mean())
     assert ms.value > 0
+
+
+def _read_png_rgb8(path):
+    """Minimal PNG reader for the test: 8-bit RGB, non-interlaced, filter type 0 rows; checks every chunk CRC."""
+    import struct
+    import zlib
+    data = open(path, "rb").read()
+    assert data[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, idat, w, h = 8, b"", 0, 0
+    while pos < len(data):
+        n, typ = struct.unpack(">I4s", data[pos:pos + 8])
+        body = data[pos + 8:pos + 8 + n]
+        assert struct.unpack(">I", data[pos + 8 + n:pos + 12 + n])[0] == zlib.crc32(typ + body) & 0xFFFFFFFF
+        if typ == b"IHDR":
+            w, h, depth, ctype, comp, flt, inter = struct.unpack(">IIBBBBB", body)
+            assert (depth, ctype, comp, flt, inter) == (8, 2, 0, 0, 0)
+        elif typ == b"IDAT":
+            idat += body
+        pos += 12 + n
+    raw = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(h, 1 + 3 * w)   # zlib verifies the Adler-32
+    assert (raw[:, 0] == 0).all()
+    return raw[:, 1:].reshape(h, w, 3)
+
+
+@pytest.mark.gpu
+def test_cpp_frame_sinks_png_and_ppm(host, grt, tmp_path, monkeypatch):
+    """Headless frame sink: the PNG and PPM files hold exactly the frame the facade returned."""
+    props = grt.synth_ply_properties(3000, 80)
+    path = str(tmp_path / "s.ply")
+    grt.write_ply(path, props)
+    W, H = 300, 250   # 226 KB of scanlines: more than one 64 KB stored block
+    for ext in ("png", "ppm"):
+        sink = str(tmp_path / f"frame.{ext}")
+        monkeypatch.setenv("GRT_HOST_FRAME_SINK", sink)
+        out = np.zeros((H, W, 3), np.uint8)
+        err = C.create_string_buffer(512)
+        rc = host.grtHostRenderPly(path.encode(), W, H, 3, 8, 0, out.ctypes.data_as(C.POINTER(C.c_ubyte)), None, err, 512)
+        assert rc == 0, err.value.decode()
+        assert out.max() > 0
+        if ext == "png":
+            img = _read_png_rgb8(sink)
+        else:
+            blob = open(sink, "rb").read()
+            hdr = f"P6\n{W} {H}\n255\n".encode()
+            assert blob.startswith(hdr)
+            img = np.frombuffer(blob[len(hdr):], np.uint8).reshape(H, W, 3)
+        assert np.array_equal(img, out)
