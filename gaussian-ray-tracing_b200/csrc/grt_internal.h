@@ -8,7 +8,10 @@
 namespace grt {
 
 constexpr int WIDE = 8;            // children per wide node
-constexpr int LEAF_MAX = 1;        // proxies (or triangles) per leaf child
+#ifndef GRT_LEAF_MAX
+#define GRT_LEAF_MAX 1
+#endif
+constexpr int LEAF_MAX = GRT_LEAF_MAX;  // proxies (or triangles) per leaf child: runs of 1..LEAF_MAX Morton-consecutive records (<= 8)
 constexpr uint32_t CHILD_EMPTY = 0xFFFFFFFFu;
 constexpr uint32_t CHILD_LEAF = 0x80000000u;  // leaf: CHILD_LEAF | (count-1) << 28 | start (28 bits)
 constexpr uint32_t INVALID_ID = 0xFFFFFFFFu;
