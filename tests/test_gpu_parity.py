@@ -150,3 +150,43 @@ def test_facade_call_order(ctx, grt, orc, tmp_path):
     assert not np.array_equal(img0, img1)
     tr.removePrimitive()
     assert tr.params.mesh_handle == 0
+
+
+@pytest.mark.parametrize("kind", ["needles_and_disks", "nested_huge_and_tiny"])
+def test_adversarial_scenes_parity(ctx, grt, orc, kind):
+    """Scenes built to stress the record slots' tight keys and the pending rings: extreme anisotropy with random
+    orientation (box keys far too early), and huge transparent shells around dense tiny particles (exit events that
+    stay pending across the whole traversal).  Same acceptance bar, plus exact hit-ID sequences on a pixel block."""
+    rng = np.random.default_rng(7 if kind == "needles_and_disks" else 8)
+    n = 6000
+    rec = np.zeros((n, 59), np.float32)
+    rec[:, 0:3] = rng.uniform(-0.8, 0.8, (n, 3)) * np.array([1.0, 0.7, 0.8])
+    q = rng.normal(size=(n, 4))
+    rec[:, 6:10] = q / np.linalg.norm(q, axis=1, keepdims=True)
+    if kind == "needles_and_disks":
+        s = np.exp(rng.normal(-3.6, 0.5, (n, 3)))
+        axis = rng.integers(0, 3, n)
+        needle = rng.random(n) < 0.5
+        for k in range(3):
+            s[:, k] *= np.where(needle, np.where(axis == k, 20.0, 1.0), np.where(axis == k, 0.05, 4.0))
+        rec[:, 3:6] = s
+        rec[:, 10] = rng.uniform(0.02, 0.9, n)
+    else:
+        big = rng.random(n) < 0.02
+        rec[:, 3:6] = np.where(big[:, None], np.exp(rng.normal(-0.6, 0.2, (n, 3))), np.exp(rng.normal(-4.5, 0.4, (n, 3))))
+        rec[:, 10] = np.where(big, rng.uniform(0.011, 0.05, n), rng.uniform(0.3, 0.99, n))
+    rec[:, 11:14] = rng.normal(0, 1.0, (n, 3))
+    rec[:, 14:59] = rng.normal(0, 0.1, (n, 45))
+    W, H = 160, 120
+    cam = grt.default_camera(rec)
+    U, V, Wv = grt.camera_uvw(cam["eye"], cam["lookat"], cam["up"], cam["fov_y"], float(np.float32(W) / np.float32(H)))
+    P = grt.make_params(W, H, cam["eye"], U, V, Wv, sh_degree_max=3)
+    rect, tmax = (72, 52, 16, 12), 160
+    tp = np.array([(rect[1] + j) * W + rect[0] + i for j in range(rect[3]) for i in range(rect[2])], np.uint32)
+    ora = _oracle(orc, rec, P, trace_pixels=tp, trace_max=tmax)
+    gpu = gpu_render(ctx, grt, rec, P, trace_rect=rect, trace_max=tmax, counters=True)
+    assert gpu.counters["order_violations"] == 0 and gpu.counters["stack_overflow"] == 0
+    compare(gpu, ora, label=kind, max_flag_frac=0.05)
+    _check_traces(gpu, ora, rect, W, ora["flags"], tmax)
+    print(kind, "hits gathered/ray", gpu.counters["hits_gathered"] / gpu.counters["rays"], "repass", gpu.counters["lanes_repass"],
+          "dfs fallbacks", gpu.counters["warp_dfs_fallbacks"])
