@@ -8,6 +8,7 @@
 //   binary hierarchy -> bottom-up atomic refit -> level-synchronous collapse into 8-wide nodes whose
 //   leaf children are runs of <= LEAF_MAX Morton-consecutive records.
 // All kernels are one-time (per scene) and HBM-bound streaming passes; none is on the per-frame path.
+#include <algorithm>
 #include <cfloat>
 #include <cstdio>
 #include <vector>
@@ -25,88 +26,103 @@ namespace grt {
 static inline unsigned int cdiv(unsigned long long a, unsigned int b) { return (unsigned int)((a + b - 1) / b); }
 
 // ------------------------------------------------------------------------------------------- radix sort
+// LSD, 8 bits per pass, stable.  Per pass: (1) per-tile digit histograms + global digit totals, (2) one warp per digit turns
+// its row of tile counts into global output offsets, (3) every tile re-reads its keys and scatters them.  A tile is
+// RS_THREADS x RS_ITEMS keys, warp w of the block owning the w-th contiguous slice of it.
+#ifndef GRT_RS_ITEMS
+#define GRT_RS_ITEMS 8
+#endif
 constexpr int RS_THREADS = 256;
-constexpr int RS_ITEMS = 16;
+constexpr int RS_ITEMS = GRT_RS_ITEMS;
 constexpr int RS_TILE = RS_THREADS * RS_ITEMS;
 constexpr int RS_WARPS = RS_THREADS / 32;
 
+// ghist[digit][tile] = count, gtot[digit] += count (gtot zeroed by the host before the pass)
 __global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const uint64_t* __restrict__ keys, uint32_t n, int shift,
-                                                             uint32_t* __restrict__ ghist, uint32_t nblocks) {
+                                                             uint32_t* __restrict__ ghist, uint32_t* __restrict__ gtot, uint32_t nblocks) {
     __shared__ uint32_t h[256];
     const uint32_t tid = threadIdx.x;
     h[tid] = 0;
     __syncthreads();
     const uint64_t base = (uint64_t)blockIdx.x * RS_TILE;
-#pragma unroll 4
+#pragma unroll
     for (int r = 0; r < RS_ITEMS; ++r) {
         uint64_t i = base + (uint64_t)r * RS_THREADS + tid;
         if (i < n) atomicAdd(&h[(uint32_t)(keys[i] >> shift) & 255u], 1u);
     }
     __syncthreads();
-    ghist[(uint64_t)tid * nblocks + blockIdx.x] = h[tid];
+    const uint32_t v = h[tid];
+    ghist[(uint64_t)tid * nblocks + blockIdx.x] = v;
+    if (v) atomicAdd(&gtot[tid], v);
 }
 
-// exclusive scan of `total` counters in place, one block of 1024 threads
-__global__ void __launch_bounds__(1024) rs_scan_kernel(uint32_t* __restrict__ data, uint32_t total) {
-    __shared__ uint32_t sums[1024];
-    const uint32_t tid = threadIdx.x;
-    const uint32_t chunk = (total + 1023u) / 1024u;
-    const uint32_t b = tid * chunk;
-    const uint32_t e = min(b + chunk, total);
-    uint32_t s = 0;
-    for (uint32_t i = b; i < e; ++i) s += data[i];
-    sums[tid] = s;
-    __syncthreads();
-    // Hillis-Steele inclusive scan over 1024 partial sums
-    for (uint32_t off = 1; off < 1024; off <<= 1) {
-        uint32_t v = (tid >= off) ? sums[tid - off] : 0u;
-        __syncthreads();
-        sums[tid] += v;
-        __syncthreads();
-    }
-    uint32_t run = sums[tid] - s;  // exclusive prefix of this chunk
-    for (uint32_t i = b; i < e; ++i) {
-        uint32_t v = data[i];
-        data[i] = run;
-        run += v;
+// one warp per digit: exclusive scan of the digit's row of tile counts, offset by the total of all smaller digits
+__global__ void __launch_bounds__(RS_THREADS) rs_scan_kernel(uint32_t* __restrict__ ghist, const uint32_t* __restrict__ gtot, uint32_t nblocks) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t d = blockIdx.x * RS_WARPS + (threadIdx.x >> 5);
+    uint32_t base = 0;
+    for (uint32_t j = lane; j < d; j += 32u) base += gtot[j];
+#pragma unroll
+    for (int o = 16; o; o >>= 1) base += __shfl_xor_sync(0xFFFFFFFFu, base, o);
+    uint32_t* row = ghist + (uint64_t)d * nblocks;
+    for (uint32_t b0 = 0; b0 < nblocks; b0 += 32u) {
+        const uint32_t v = (b0 + lane < nblocks) ? row[b0 + lane] : 0u;
+        uint32_t inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+            if (lane >= (uint32_t)o) inc += t;
+        }
+        if (b0 + lane < nblocks) row[b0 + lane] = base + inc - v;
+        base += __shfl_sync(0xFFFFFFFFu, inc, 31);
     }
 }
 
 __global__ void __launch_bounds__(RS_THREADS) rs_scatter_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                                                                 uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                                                                 uint32_t n, int shift, const uint32_t* __restrict__ ghist, uint32_t nblocks) {
-    __shared__ uint32_t running[256];
-    __shared__ uint32_t cnt[RS_WARPS][256];
+    __shared__ uint32_t cnt[RS_WARPS][256];  // per-warp digit counts, then per-warp output bases
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
-    running[tid] = ghist[(uint64_t)tid * nblocks + blockIdx.x];
 #pragma unroll
     for (int w = 0; w < RS_WARPS; ++w) cnt[w][tid] = 0;
     __syncthreads();
-    const uint64_t base = (uint64_t)blockIdx.x * RS_TILE;
+    const uint64_t base = (uint64_t)blockIdx.x * RS_TILE + (uint64_t)warp * (32 * RS_ITEMS);
+    uint64_t key[RS_ITEMS];
+    uint32_t val[RS_ITEMS], off[RS_ITEMS];
+#pragma unroll
     for (int r = 0; r < RS_ITEMS; ++r) {
-        const uint64_t i = base + (uint64_t)r * RS_THREADS + tid;
+        const uint64_t i = base + (uint64_t)r * 32u + lane;
         const bool valid = i < n;
-        uint64_t key = 0;
-        uint32_t val = 0;
-        if (valid) { key = keys_in[i]; val = vals_in[i]; }
+        key[r] = 0; val[r] = 0;
+        if (valid) { key[r] = keys_in[i]; val[r] = vals_in[i]; }
+    }
+#pragma unroll
+    for (int r = 0; r < RS_ITEMS; ++r) {
+        const bool valid = base + (uint64_t)r * 32u + lane < n;
         // invalid lanes get a private pseudo-digit so they only match themselves
-        const uint32_t dgt = valid ? ((uint32_t)(key >> shift) & 255u) : (256u + lane);
+        const uint32_t dgt = valid ? ((uint32_t)(key[r] >> shift) & 255u) : (256u + lane);
         const uint32_t peers = __match_any_sync(0xFFFFFFFFu, dgt);
         const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
-        if (valid && rank == 0) cnt[warp][dgt] = __popc(peers);
-        __syncthreads();
-        if (valid) {
-            uint32_t pos = running[dgt] + rank;
-            for (uint32_t w = 0; w < warp; ++w) pos += cnt[w][dgt];
-            keys_out[pos] = key;
-            vals_out[pos] = val;
-        }
-        __syncthreads();
-        uint32_t sum = 0;
+        uint32_t old = 0;
+        if (valid && rank == 0) { old = cnt[warp][dgt]; cnt[warp][dgt] = old + __popc(peers); }
+        old = __shfl_sync(0xFFFFFFFFu, old, __ffs(peers) - 1);
+        off[r] = old + rank;
+        __syncwarp();
+    }
+    __syncthreads();
+    {   // digit tid: warp w's keys of this digit start at tile offset + counts of the warps before it
+        uint32_t run = ghist[(uint64_t)tid * nblocks + blockIdx.x];
 #pragma unroll
-        for (int w = 0; w < RS_WARPS; ++w) { sum += cnt[w][tid]; cnt[w][tid] = 0; }
-        running[tid] += sum;
-        __syncthreads();
+        for (int w = 0; w < RS_WARPS; ++w) { const uint32_t c = cnt[w][tid]; cnt[w][tid] = run; run += c; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < RS_ITEMS; ++r) {
+        if (base + (uint64_t)r * 32u + lane < n) {
+            const uint32_t pos = cnt[warp][(uint32_t)(key[r] >> shift) & 255u] + off[r];
+            keys_out[pos] = key[r];
+            vals_out[pos] = val[r];
+        }
     }
 }
 
@@ -140,15 +156,18 @@ int radix_sort_pairs(uint64_t* d_keys, uint64_t* d_keys_tmp, uint32_t* d_vals, u
     *result_in_tmp = false;
     if (n == 0) return 0;
     const uint32_t nblocks = cdiv(n, RS_TILE);
-    uint32_t* d_hist = scratch ? static_cast<uint32_t*>(scratch->get(sizeof(uint32_t) * 256ull * nblocks)) : nullptr;
+    const size_t hist_bytes = sizeof(uint32_t) * (256ull * nblocks + 8ull * 256ull);  // tile counts + 8 passes of digit totals
+    uint32_t* d_hist = scratch ? static_cast<uint32_t*>(scratch->get(hist_bytes)) : nullptr;
     const bool own_hist = d_hist == nullptr;
-    if (own_hist) CK(cudaMalloc(&d_hist, sizeof(uint32_t) * 256ull * nblocks));
+    if (own_hist) CK(cudaMalloc(&d_hist, hist_bytes));
+    uint32_t* d_tot = d_hist + 256ull * nblocks;
+    CK(cudaMemsetAsync(d_tot, 0, sizeof(uint32_t) * 8 * 256, stream));
     uint64_t* kin = d_keys; uint64_t* kout = d_keys_tmp;
     uint32_t* vin = d_vals; uint32_t* vout = d_vals_tmp;
     for (int pass = 0; pass < 8; ++pass) {
         const int shift = pass * 8;
-        rs_hist_kernel<<<nblocks, RS_THREADS, 0, stream>>>(kin, n, shift, d_hist, nblocks);
-        rs_scan_kernel<<<1, 1024, 0, stream>>>(d_hist, 256u * nblocks);
+        rs_hist_kernel<<<nblocks, RS_THREADS, 0, stream>>>(kin, n, shift, d_hist, d_tot + 256 * pass, nblocks);
+        rs_scan_kernel<<<256 / RS_WARPS, RS_THREADS, 0, stream>>>(d_hist, d_tot + 256 * pass, nblocks);
         rs_scatter_kernel<<<nblocks, RS_THREADS, 0, stream>>>(kin, vin, kout, vout, n, shift, d_hist, nblocks);
         *launches += 3;
         std::swap(kin, kout);
@@ -179,35 +198,53 @@ __host__ __device__ __forceinline__ float dec_f(uint32_t e) {
 }
 
 // bounds[0..2] = encoded min of box centres, bounds[3..5] = encoded max, bounds[6] = live count
-__global__ void bounds_kernel(const float4* __restrict__ lo, const float4* __restrict__ hi, uint32_t n, uint32_t* __restrict__ bounds) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+// (grid-stride, one set of atomics per block: min / max / count do not depend on the order)
+__global__ void __launch_bounds__(256) bounds_kernel(const float4* __restrict__ lo, const float4* __restrict__ hi, uint32_t n,
+                                                     uint32_t* __restrict__ bounds) {
+    __shared__ float sm[8][6];
+    __shared__ uint32_t sl[8];
     float c[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, C[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
     uint32_t live = 0;
-    if (i < n) {
-        float4 a = lo[i], b = hi[i];
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 a = lo[i], b = hi[i];
         if (a.x <= b.x) {
-            live = 1;
-            c[0] = C[0] = 0.5f * (a.x + b.x);
-            c[1] = C[1] = 0.5f * (a.y + b.y);
-            c[2] = C[2] = 0.5f * (a.z + b.z);
+            live++;
+            const float m[3] = {0.5f * (a.x + b.x), 0.5f * (a.y + b.y), 0.5f * (a.z + b.z)};
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { c[k] = fminf(c[k], m[k]); C[k] = fmaxf(C[k], m[k]); }
         }
     }
 #pragma unroll
-    for (int k = 0; k < 3; ++k) {
+    for (int o = 16; o; o >>= 1) {
 #pragma unroll
-        for (int o = 16; o; o >>= 1) {
+        for (int k = 0; k < 3; ++k) {
             c[k] = fminf(c[k], __shfl_xor_sync(0xFFFFFFFFu, c[k], o));
             C[k] = fmaxf(C[k], __shfl_xor_sync(0xFFFFFFFFu, C[k], o));
         }
+        live += __shfl_xor_sync(0xFFFFFFFFu, live, o);
     }
-    const uint32_t nlive = __popc(__ballot_sync(0xFFFFFFFFu, live));
-    if ((threadIdx.x & 31u) == 0 && nlive) {
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    if (lane == 0) {
 #pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            atomicMin(&bounds[k], enc_f(c[k]));
-            atomicMax(&bounds[3 + k], enc_f(C[k]));
+        for (int k = 0; k < 3; ++k) { sm[warp][k] = c[k]; sm[warp][3 + k] = C[k]; }
+        sl[warp] = live;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t nl = 0;
+        for (int w = 0; w < 8; ++w) {
+            nl += sl[w];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { c[k] = fminf(c[k], sm[w][k]); C[k] = fmaxf(C[k], sm[w][3 + k]); }
         }
-        atomicAdd(&bounds[6], nlive);
+        if (nl) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                atomicMin(&bounds[k], enc_f(c[k]));
+                atomicMax(&bounds[3 + k], enc_f(C[k]));
+            }
+            atomicAdd(&bounds[6], nl);
+        }
     }
 }
 
@@ -327,62 +364,69 @@ __device__ __forceinline__ void write_child(WideNode* nd, int k, float4 lo, floa
     nd->pad[k] = 0;
 }
 
-__global__ void collapse_kernel(BinTree T, const uint2* __restrict__ q_in, uint32_t n_in, uint2* __restrict__ q_out, uint32_t* __restrict__ n_out,
-                                uint32_t* __restrict__ node_counter, WideNode* __restrict__ nodes) {
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= n_in) return;
-    const uint32_t b = q_in[t].x, w = q_in[t].y;
-    uint32_t slots[WIDE];
-    int ns = 2;
-    slots[0] = T.left[b];
-    slots[1] = T.right[b];
-    // Open the largest-area child until the node is full.  A subtree of more than WIDE records is split into its
-    // two binary children; a smaller one is only opened if ALL its records fit into the free slots (it is then
-    // flattened into single-record leaf children), so that the bottom of the tree is made of well-filled nodes
-    // instead of chains of 2- and 3-child nodes.
-    while (ns < WIDE) {
-        int best = -1;
-        float bestA = -1.0f;
-        for (int k = 0; k < ns; ++k) {
-            const uint32_t id = slots[k];
-            if (id >= T.n - 1) continue;
-            const uint32_t c = T.count(id);
-            if (c <= (uint32_t)LEAF_MAX) continue;
-            if (LEAF_MAX == 1 && c <= (uint32_t)WIDE && ns - 1 + (int)c > WIDE) continue;
-            const float4 a = T.blo[id], d = T.bhi[id];
-            const float ex = d.x - a.x, ey = d.y - a.y, ez = d.z - a.z;
-            const float area = ex * ey + ey * ez + ez * ex;
-            if (area > bestA) { bestA = area; best = k; }
-        }
-        if (best < 0) break;
-        const uint32_t id = slots[best];
-        const uint32_t c = T.count(id);
-        if (LEAF_MAX == 1 && c <= (uint32_t)WIDE) {
-            const uint32_t s0 = T.start(id);
-            slots[best] = T.n - 1 + s0;
-            for (uint32_t k = 1; k < c; ++k) slots[ns++] = T.n - 1 + s0 + k;
-        } else {
-            slots[best] = T.left[id];
-            slots[ns++] = T.right[id];
-        }
-    }
-    WideNode* nd = &nodes[w];
-    for (int k = 0; k < WIDE; ++k) {
-        if (k < ns) {
-            const uint32_t id = slots[k];
-            const uint32_t c = T.count(id);
-            uint32_t ref;
-            if (c <= (uint32_t)LEAF_MAX) {
-                ref = CHILD_LEAF | ((c - 1u) << 28) | T.start(id);
-            } else {
-                const uint32_t wi = atomicAdd(node_counter, 1u);
-                const uint32_t o = atomicAdd(n_out, 1u);
-                q_out[o] = make_uint2(id, wi);
-                ref = wi;
+// One level: work items (binary node, wide-node index) come from q_in, the items of the next level go to q_out.  The item
+// counts live on the device (lvl[0] in, lvl[1] out) so that several levels can be queued without a host round trip; a wide
+// node whose index does not fit into `cap` is counted but not written (the host then repeats the collapse into a larger array).
+__global__ void __launch_bounds__(128) collapse_kernel(BinTree T, const uint2* __restrict__ q_in, uint2* __restrict__ q_out,
+                                                       uint32_t* __restrict__ lvl, uint32_t* __restrict__ node_counter,
+                                                       WideNode* __restrict__ nodes, uint32_t cap) {
+    const uint32_t n_in = lvl[0];
+    uint32_t* const n_out = lvl + 1;
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n_in; t += gridDim.x * blockDim.x) {
+        const uint32_t b = q_in[t].x, w = q_in[t].y;
+        uint32_t slots[WIDE];
+        int ns = 2;
+        slots[0] = T.left[b];
+        slots[1] = T.right[b];
+        // Open the largest-area child until the node is full.  A subtree of more than WIDE records is split into its
+        // two binary children; a smaller one is only opened if ALL its records fit into the free slots (it is then
+        // flattened into single-record leaf children), so that the bottom of the tree is made of well-filled nodes
+        // instead of chains of 2- and 3-child nodes.
+        while (ns < WIDE) {
+            int best = -1;
+            float bestA = -1.0f;
+            for (int k = 0; k < ns; ++k) {
+                const uint32_t id = slots[k];
+                if (id >= T.n - 1) continue;
+                const uint32_t c = T.count(id);
+                if (c <= (uint32_t)LEAF_MAX) continue;
+                if (LEAF_MAX == 1 && c <= (uint32_t)WIDE && ns - 1 + (int)c > WIDE) continue;
+                const float4 a = T.blo[id], d = T.bhi[id];
+                const float ex = d.x - a.x, ey = d.y - a.y, ez = d.z - a.z;
+                const float area = ex * ey + ey * ez + ez * ex;
+                if (area > bestA) { bestA = area; best = k; }
             }
-            write_child(nd, k, T.blo[id], T.bhi[id], ref);
-        } else {
-            write_child(nd, k, make_float4(INFINITY, INFINITY, INFINITY, 0.f), make_float4(-INFINITY, -INFINITY, -INFINITY, 0.f), CHILD_EMPTY);
+            if (best < 0) break;
+            const uint32_t id = slots[best];
+            const uint32_t c = T.count(id);
+            if (LEAF_MAX == 1 && c <= (uint32_t)WIDE) {
+                const uint32_t s0 = T.start(id);
+                slots[best] = T.n - 1 + s0;
+                for (uint32_t k = 1; k < c; ++k) slots[ns++] = T.n - 1 + s0 + k;
+            } else {
+                slots[best] = T.left[id];
+                slots[ns++] = T.right[id];
+            }
+        }
+        const bool fits = w < cap;
+        WideNode* nd = &nodes[fits ? w : 0u];
+        for (int k = 0; k < WIDE; ++k) {
+            if (k < ns) {
+                const uint32_t id = slots[k];
+                const uint32_t c = T.count(id);
+                uint32_t ref;
+                if (c <= (uint32_t)LEAF_MAX) {
+                    ref = CHILD_LEAF | ((c - 1u) << 28) | T.start(id);
+                } else {
+                    const uint32_t wi = atomicAdd(node_counter, 1u);
+                    const uint32_t o = atomicAdd(n_out, 1u);
+                    q_out[o] = make_uint2(id, wi);
+                    ref = wi;
+                }
+                if (fits) write_child(nd, k, T.blo[id], T.bhi[id], ref);
+            } else if (fits) {
+                write_child(nd, k, make_float4(INFINITY, INFINITY, INFINITY, 0.f), make_float4(-INFINITY, -INFINITY, -INFINITY, 0.f), CHILD_EMPTY);
+            }
         }
     }
 }
@@ -429,7 +473,7 @@ int lbvh_build(const float4* d_lo, const float4* d_hi, uint32_t n, cudaStream_t 
     CK(bounds.alloc(8 * sizeof(uint32_t)));
     const uint32_t h_init[8] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u, 0u, 0u, 0u};
     CK(cudaMemcpyAsync(bounds.p, h_init, sizeof(h_init), cudaMemcpyHostToDevice, stream));
-    bounds_kernel<<<cdiv(n, TB), TB, 0, stream>>>(d_lo, d_hi, n, bounds.as<uint32_t>());
+    bounds_kernel<<<std::min(cdiv(n, 256), 148u * 8u), 256, 0, stream>>>(d_lo, d_hi, n, bounds.as<uint32_t>());
     ++*launches;
     CK(keys.alloc(sizeof(uint64_t) * n));
     CK(keys2.alloc(sizeof(uint64_t) * n));
@@ -483,37 +527,60 @@ int lbvh_build(const float4* d_lo, const float4* d_hi, uint32_t n, cudaStream_t 
 
     // collapse, level by level.  Upper bound on wide nodes: every wide node but the root is a binary
     // internal node with > LEAF_MAX prims, and two such nodes never share a leaf run, so <= nl.
+    // The levels are queued COLLAPSE_CHUNK at a time with their item counts on the device; the nodes are written
+    // straight into the caller's array when it is likely to be large enough (checked afterwards), else into scratch.
     const uint32_t max_nodes = nl;
-    CK(wide_tmp.alloc(sizeof(WideNode) * (size_t)max_nodes));
+    constexpr int COLLAPSE_CHUNK = 16;
     CK(qa.alloc(sizeof(uint2) * (size_t)max_nodes));
     CK(qb.alloc(sizeof(uint2) * (size_t)max_nodes));
-    CK(ctr.alloc(2 * sizeof(uint32_t)));  // [0] = node counter, [1] = n_out
-    const uint2 root_item = make_uint2(0u, 0u);
-    CK(cudaMemcpyAsync(qa.p, &root_item, sizeof(uint2), cudaMemcpyHostToDevice, stream));
-    uint32_t h_ctr[2] = {1u, 0u};
-    CK(cudaMemcpyAsync(ctr.p, h_ctr, sizeof(h_ctr), cudaMemcpyHostToDevice, stream));
+    CK(ctr.alloc((COLLAPSE_CHUNK + 2) * sizeof(uint32_t)));  // [0] = node counter, [1..] = items per level of the chunk
     BinTree T{left.as<uint32_t>(), right.as<uint32_t>(), first.as<uint32_t>(), last.as<uint32_t>(), blo.as<float4>(), bhi.as<float4>(), nl};
-    uint32_t n_in = 1, levels = 0;
-    uint2* qi = qa.as<uint2>();
-    uint2* qo = qb.as<uint2>();
-    while (n_in) {
-        collapse_kernel<<<cdiv(n_in, 128), 128, 0, stream>>>(T, qi, n_in, qo, ctr.as<uint32_t>() + 1, ctr.as<uint32_t>(), wide_tmp.as<WideNode>());
-        ++*launches;
-        ++levels;
-        CK(cudaMemcpyAsync(h_ctr, ctr.p, sizeof(h_ctr), cudaMemcpyDeviceToHost, stream));
-        CK(cudaStreamSynchronize(stream));
-        n_in = h_ctr[1];
-        const uint32_t zero = 0;
-        CK(cudaMemcpyAsync(ctr.as<uint32_t>() + 1, &zero, 4, cudaMemcpyHostToDevice, stream));
-        std::swap(qi, qo);
-        if (levels > 4096) return (int)cudaErrorUnknown;
+    const uint32_t grid = std::min(cdiv(max_nodes, 128), 148u * 8u);
+    uint32_t n_nodes = 0, levels = 0;
+    WideNode* target = (reuse_nodes && reuse_cap >= nl / 6u + 16u) ? reuse_nodes : nullptr;
+    uint32_t cap = target ? reuse_cap : max_nodes;
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        if (!target) {
+            CK(wide_tmp.alloc(sizeof(WideNode) * (size_t)max_nodes));
+            target = wide_tmp.as<WideNode>();
+            cap = max_nodes;
+        }
+        const uint2 root_item = make_uint2(0u, 0u);
+        CK(cudaMemcpyAsync(qa.p, &root_item, sizeof(uint2), cudaMemcpyHostToDevice, stream));
+        uint32_t h_ctr[COLLAPSE_CHUNK + 2] = {1u, 1u};  // one node (the root) allocated, one item at level 0
+        CK(cudaMemcpyAsync(ctr.p, h_ctr, sizeof(h_ctr), cudaMemcpyHostToDevice, stream));
+        uint2* qi = qa.as<uint2>();
+        uint2* qo = qb.as<uint2>();
+        levels = 0;
+        for (;;) {
+            for (int l = 0; l < COLLAPSE_CHUNK; ++l) {
+                collapse_kernel<<<grid, 128, 0, stream>>>(T, qi, qo, ctr.as<uint32_t>() + 1 + l, ctr.as<uint32_t>(), target, cap);
+                std::swap(qi, qo);
+            }
+            *launches += COLLAPSE_CHUNK;
+            CK(cudaMemcpyAsync(h_ctr, ctr.p, sizeof(h_ctr), cudaMemcpyDeviceToHost, stream));
+            CK(cudaStreamSynchronize(stream));
+            for (int l = 0; l < COLLAPSE_CHUNK; ++l) levels += h_ctr[1 + l] != 0u;
+            if (h_ctr[1 + COLLAPSE_CHUNK] == 0u) break;
+            if (levels > 4096) return (int)cudaErrorUnknown;
+            uint32_t next[COLLAPSE_CHUNK + 2] = {h_ctr[0], h_ctr[1 + COLLAPSE_CHUNK]};
+            CK(cudaMemcpyAsync(ctr.p, next, sizeof(next), cudaMemcpyHostToDevice, stream));
+        }
+        n_nodes = h_ctr[0];
+        if (n_nodes <= cap) break;
+        target = nullptr;  // the caller's array was too small after all: once more, into scratch
     }
     CK(cudaGetLastError());
-    const uint32_t n_nodes = h_ctr[0];
-    WideNode* nodes = n_nodes <= reuse_cap ? reuse_nodes : nullptr;
-    if (!nodes) CK(cudaMalloc(&nodes, sizeof(WideNode) * (size_t)n_nodes));
-    CK(cudaMemcpyAsync(nodes, wide_tmp.p, sizeof(WideNode) * (size_t)n_nodes, cudaMemcpyDeviceToDevice, stream));
-    CK(cudaStreamSynchronize(stream));
+    WideNode* nodes = target;
+    if (target != reuse_nodes) {
+        nodes = n_nodes <= reuse_cap ? reuse_nodes : nullptr;
+        if (!nodes) {
+            out->nodes_cap = n_nodes + n_nodes / 8u + 16u;  // headroom: a slightly different particle set rebuilds in place
+            CK(cudaMalloc(&nodes, sizeof(WideNode) * (size_t)out->nodes_cap));
+        }
+        CK(cudaMemcpyAsync(nodes, target, sizeof(WideNode) * (size_t)n_nodes, cudaMemcpyDeviceToDevice, stream));
+        CK(cudaStreamSynchronize(stream));
+    }
     out->nodes = nodes;
     out->n_nodes = n_nodes;
     out->levels = levels;

@@ -424,7 +424,7 @@ int grtBuildParticleAccel(grtContext* c, void* stream_v, uint64_t* handle_out, v
     if (res.nodes && res.nodes != c->p_nodes) {
         cudaFree(c->p_nodes);
         c->p_nodes = res.nodes;
-        c->p_nodes_cap = res.n_nodes;
+        c->p_nodes_cap = res.nodes_cap ? res.nodes_cap : res.n_nodes;
     }
     c->p_live = res.n_live; c->p_nnodes = res.n_nodes; c->p_levels = res.levels;
     if (res.n_live) {

@@ -97,8 +97,9 @@ struct BuildScratch {
     void release();               // free the block
 };
 struct LbvhResult {
-    WideNode* nodes = nullptr;  // cudaMalloc'd (exact size), or reuse_nodes when the tree fits into it
+    WideNode* nodes = nullptr;  // cudaMalloc'd (nodes_cap entries), or reuse_nodes when the tree fits into it
     uint32_t n_nodes = 0;
+    uint32_t nodes_cap = 0;     // capacity of a freshly cudaMalloc'd `nodes` (0 when reuse_nodes was kept)
     uint32_t* perm = nullptr;   // sorted position -> input index, n_live entries valid (n entries; scratch unless perm_owned)
     bool perm_owned = true;     // perm was cudaMalloc'd: the caller frees it
     WideNode* reuse_nodes = nullptr;  // in: a node array of an earlier build the caller is willing to overwrite
