@@ -364,6 +364,35 @@ __device__ __forceinline__ void write_child(WideNode* nd, int k, float4 lo, floa
     nd->pad[k] = 0;
 }
 
+// What the collapse needs to know about a candidate child: fetched once when the child appears (all loads independent),
+// so that opening a child costs one round of memory latency instead of one per candidate per step.
+struct Slot {
+    uint32_t id, cnt, first, l, r;
+    float area;
+};
+__device__ __forceinline__ Slot load_slot(const BinTree& T, uint32_t id) {
+    Slot s;
+    s.id = id;
+    if (id >= T.n - 1) {
+        s.cnt = 1u; s.first = id - (T.n - 1); s.l = s.r = 0u; s.area = -1.0f;
+        return s;
+    }
+    const uint32_t f = T.first[id], la = T.last[id];
+    s.l = T.left[id];
+    s.r = T.right[id];
+    const float4 a = T.blo[id], d = T.bhi[id];
+    const float ex = d.x - a.x, ey = d.y - a.y, ez = d.z - a.z;
+    s.area = ex * ey + ey * ez + ez * ex;
+    s.cnt = la - f + 1u;
+    s.first = f;
+    return s;
+}
+__device__ __forceinline__ Slot leaf_slot(const BinTree& T, uint32_t j) {
+    Slot s;
+    s.id = T.n - 1 + j; s.cnt = 1u; s.first = j; s.l = s.r = 0u; s.area = -1.0f;
+    return s;
+}
+
 // One level: work items (binary node, wide-node index) come from q_in, the items of the next level go to q_out.  The item
 // counts live on the device (lvl[0] in, lvl[1] out) so that several levels can be queued without a host round trip; a wide
 // node whose index does not fit into `cap` is counted but not written (the host then repeats the collapse into a larger array).
@@ -374,10 +403,13 @@ __global__ void __launch_bounds__(128) collapse_kernel(BinTree T, const uint2* _
     uint32_t* const n_out = lvl + 1;
     for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n_in; t += gridDim.x * blockDim.x) {
         const uint32_t b = q_in[t].x, w = q_in[t].y;
-        uint32_t slots[WIDE];
+        Slot sl[WIDE];
         int ns = 2;
-        slots[0] = T.left[b];
-        slots[1] = T.right[b];
+        {
+            const uint32_t l = T.left[b], r = T.right[b];
+            sl[0] = load_slot(T, l);
+            sl[1] = load_slot(T, r);
+        }
         // Open the largest-area child until the node is full.  A subtree of more than WIDE records is split into its
         // two binary children; a smaller one is only opened if ALL its records fit into the free slots (it is then
         // flattened into single-record leaf children), so that the bottom of the tree is made of well-filled nodes
@@ -385,43 +417,62 @@ __global__ void __launch_bounds__(128) collapse_kernel(BinTree T, const uint2* _
         while (ns < WIDE) {
             int best = -1;
             float bestA = -1.0f;
-            for (int k = 0; k < ns; ++k) {
-                const uint32_t id = slots[k];
-                if (id >= T.n - 1) continue;
-                const uint32_t c = T.count(id);
-                if (c <= (uint32_t)LEAF_MAX) continue;
+#pragma unroll
+            for (int k = 0; k < WIDE; ++k) {
+                if (k >= ns) continue;
+                const uint32_t c = sl[k].cnt;
+                if (c <= (uint32_t)LEAF_MAX) continue;  // (covers single records: cnt 1)
                 if (LEAF_MAX == 1 && c <= (uint32_t)WIDE && ns - 1 + (int)c > WIDE) continue;
-                const float4 a = T.blo[id], d = T.bhi[id];
-                const float ex = d.x - a.x, ey = d.y - a.y, ez = d.z - a.z;
-                const float area = ex * ey + ey * ez + ez * ex;
-                if (area > bestA) { bestA = area; best = k; }
+                if (sl[k].area > bestA) { bestA = sl[k].area; best = k; }
             }
             if (best < 0) break;
-            const uint32_t id = slots[best];
-            const uint32_t c = T.count(id);
-            if (LEAF_MAX == 1 && c <= (uint32_t)WIDE) {
-                const uint32_t s0 = T.start(id);
-                slots[best] = T.n - 1 + s0;
-                for (uint32_t k = 1; k < c; ++k) slots[ns++] = T.n - 1 + s0 + k;
+            Slot o;
+#pragma unroll
+            for (int k = 0; k < WIDE; ++k) if (k == best) o = sl[k];
+            Slot na, nb;
+            bool flat = LEAF_MAX == 1 && o.cnt <= (uint32_t)WIDE;
+            if (!flat) {
+                na = load_slot(T, o.l);
+                nb = load_slot(T, o.r);
             } else {
-                slots[best] = T.left[id];
-                slots[ns++] = T.right[id];
+                na = leaf_slot(T, o.first);
             }
+#pragma unroll
+            for (int k = 0; k < WIDE; ++k) if (k == best) sl[k] = na;
+            if (!flat) {
+#pragma unroll
+                for (int k = 0; k < WIDE; ++k) if (k == ns) sl[k] = nb;
+                ++ns;
+            } else {
+                for (uint32_t j = 1; j < o.cnt; ++j) {
+                    const Slot lf = leaf_slot(T, o.first + j);
+#pragma unroll
+                    for (int k = 0; k < WIDE; ++k) if (k == ns) sl[k] = lf;
+                    ++ns;
+                }
+            }
+        }
+        // children that stay subtrees become work items of the next level: one reservation per node, not per child
+        uint32_t m = 0;
+#pragma unroll
+        for (int k = 0; k < WIDE; ++k) m += (k < ns && sl[k].cnt > (uint32_t)LEAF_MAX) ? 1u : 0u;
+        uint32_t wi = 0, qo = 0;
+        if (m) {
+            wi = atomicAdd(node_counter, m);
+            qo = atomicAdd(n_out, m);
         }
         const bool fits = w < cap;
         WideNode* nd = &nodes[fits ? w : 0u];
+#pragma unroll
         for (int k = 0; k < WIDE; ++k) {
             if (k < ns) {
-                const uint32_t id = slots[k];
-                const uint32_t c = T.count(id);
+                const uint32_t id = sl[k].id;
                 uint32_t ref;
-                if (c <= (uint32_t)LEAF_MAX) {
-                    ref = CHILD_LEAF | ((c - 1u) << 28) | T.start(id);
+                if (sl[k].cnt <= (uint32_t)LEAF_MAX) {
+                    ref = CHILD_LEAF | ((sl[k].cnt - 1u) << 28) | sl[k].first;
                 } else {
-                    const uint32_t wi = atomicAdd(node_counter, 1u);
-                    const uint32_t o = atomicAdd(n_out, 1u);
-                    q_out[o] = make_uint2(id, wi);
-                    ref = wi;
+                    q_out[qo++] = make_uint2(id, wi);
+                    ref = wi++;
                 }
                 if (fits) write_child(nd, k, T.blo[id], T.bhi[id], ref);
             } else if (fits) {
@@ -661,8 +712,21 @@ __global__ void particle_boxes_kernel(const float* __restrict__ raw, const float
 __global__ void particle_gather_kernel(const float* __restrict__ raw, const float* __restrict__ s_arr, const uint32_t* __restrict__ perm,
                                        uint32_t n_live, PRec* __restrict__ recs, float4* __restrict__ sh) {
     const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t i = j < n_live ? perm[j] : 0u;
+    // SH coefficients: the warp copies the 32 x 48 floats of its particles with consecutive lanes on consecutive floats, so
+    // that both the reads (within a 192-byte row segment) and the writes (one contiguous 6 KB block) are coalesced
+    {
+        const uint32_t j0 = j - lane;
+        const uint32_t cnt = min(32u, n_live > j0 ? n_live - j0 : 0u) * (uint32_t)(SH_F4 * 4);
+        float* o = reinterpret_cast<float*>(sh + (size_t)j0 * SH_F4);
+#pragma unroll 4
+        for (uint32_t e = lane; e < 32u * (uint32_t)(SH_F4 * 4); e += 32u) {
+            const uint32_t src = __shfl_sync(0xFFFFFFFFu, i, e / (uint32_t)(SH_F4 * 4));
+            if (e < cnt) o[e] = __ldg(raw + (size_t)src * RAW_FLOATS + 11u + e % (uint32_t)(SH_F4 * 4));
+        }
+    }
     if (j >= n_live) return;
-    const uint32_t i = perm[j];
     const float* p = raw + (size_t)i * RAW_FLOATS;
     const M3 R = mat3_cast_rn(p[6], p[7], p[8], p[9]);
     float A[3][3];
@@ -678,9 +742,6 @@ __global__ void particle_gather_kernel(const float* __restrict__ raw, const floa
     rec.q2 = make_float4(A[2][2], p[0], p[1], p[2]);
     rec.q3 = make_float4(s_arr[i], p[10], __uint_as_float(i), 0.f);
     recs[j] = rec;
-    float4* o = sh + (size_t)j * SH_F4;
-#pragma unroll
-    for (int k = 0; k < SH_F4; ++k) o[k] = make_float4(p[11 + 4 * k], p[12 + 4 * k], p[13 + 4 * k], p[14 + 4 * k]);
 }
 
 int particles_compute_boxes(const void* d_particles236, const float* d_s, uint32_t n, float4* d_lo, float4* d_hi, cudaStream_t stream,

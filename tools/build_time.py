@@ -14,11 +14,15 @@ grt = importlib.import_module("gaussian-ray-tracing_b200")
 def main():
     out = []
     ctx = grt.Context(0)
-    for n, seed in [(100_000, 1001), (1_000_000, 1002), (6_000_000, 1003)]:
+    sizes = [(100_000, 1001), (1_000_000, 1002), (6_000_000, 1003)]
+    if len(sys.argv) > 1:
+        sizes = [s for s in sizes if str(s[0]) in sys.argv[1:]]
+    reps = 3 if "--short" in sys.argv else 8
+    for n, seed in sizes:
         rec = grt.activate(grt.synth_ply_properties(n, seed))
         ctx.set_particles(rec, 0.01)
         ms, wall = [], []
-        for _ in range(8):
+        for _ in range(reps):
             t = time.perf_counter()
             ctx.build_particle_accel()
             wall.append((time.perf_counter() - t) * 1e3)
