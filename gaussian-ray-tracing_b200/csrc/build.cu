@@ -60,45 +60,75 @@ __global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const uint64_t* __r
 __global__ void __launch_bounds__(RS_THREADS) rs_scan_kernel(uint32_t* __restrict__ ghist, const uint32_t* __restrict__ gtot, uint32_t nblocks) {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t d = blockIdx.x * RS_WARPS + (threadIdx.x >> 5);
+    uint32_t* row = ghist + (uint64_t)d * nblocks;
+    constexpr int PRE = 16;  // rows of up to 32 * PRE tiles are fetched with all loads in flight at once
+    uint32_t v[PRE];
+    if (nblocks <= 32u * PRE) {
+#pragma unroll
+        for (int c = 0; c < PRE; ++c) v[c] = (c * 32u + lane < nblocks) ? row[c * 32u + lane] : 0u;
+    }
     uint32_t base = 0;
     for (uint32_t j = lane; j < d; j += 32u) base += gtot[j];
 #pragma unroll
     for (int o = 16; o; o >>= 1) base += __shfl_xor_sync(0xFFFFFFFFu, base, o);
-    uint32_t* row = ghist + (uint64_t)d * nblocks;
+    if (nblocks <= 32u * PRE) {
+#pragma unroll
+        for (int c = 0; c < PRE; ++c) {
+            if (c * 32u < nblocks) {
+                uint32_t inc = v[c];
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+                    if (lane >= (uint32_t)o) inc += t;
+                }
+                if (c * 32u + lane < nblocks) row[c * 32u + lane] = base + inc - v[c];
+                base += __shfl_sync(0xFFFFFFFFu, inc, 31);
+            }
+        }
+        return;
+    }
     for (uint32_t b0 = 0; b0 < nblocks; b0 += 32u) {
-        const uint32_t v = (b0 + lane < nblocks) ? row[b0 + lane] : 0u;
-        uint32_t inc = v;
+        const uint32_t x = (b0 + lane < nblocks) ? row[b0 + lane] : 0u;
+        uint32_t inc = x;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
             if (lane >= (uint32_t)o) inc += t;
         }
-        if (b0 + lane < nblocks) row[b0 + lane] = base + inc - v;
+        if (b0 + lane < nblocks) row[b0 + lane] = base + inc - x;
         base += __shfl_sync(0xFFFFFFFFu, inc, 31);
     }
 }
 
+// Scatter of one tile.  The keys are first put into digit order inside shared memory (stable: warp slice, round, lane), then
+// written out by consecutive threads, so that the keys of one digit -- which are consecutive in the output -- leave as
+// coalesced runs instead of 32 scattered 8-byte stores per warp.
 __global__ void __launch_bounds__(RS_THREADS) rs_scatter_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                                                                 uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                                                                 uint32_t n, int shift, const uint32_t* __restrict__ ghist, uint32_t nblocks) {
-    __shared__ uint32_t cnt[RS_WARPS][256];  // per-warp digit counts, then per-warp output bases
+    __shared__ uint32_t cnt[RS_WARPS][256];  // per-warp digit counts, then the warp's start inside the tile's digit run
+    __shared__ uint32_t delta[256];          // global start of the tile's digit run minus its start inside the sorted tile
+    __shared__ uint32_t wsum[RS_WARPS];
+    __shared__ uint64_t skey[RS_TILE];
+    __shared__ uint32_t sval[RS_TILE];
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
 #pragma unroll
     for (int w = 0; w < RS_WARPS; ++w) cnt[w][tid] = 0;
     __syncthreads();
-    const uint64_t base = (uint64_t)blockIdx.x * RS_TILE + (uint64_t)warp * (32 * RS_ITEMS);
+    const uint64_t tile0 = (uint64_t)blockIdx.x * RS_TILE;
+    const uint32_t nv = (uint32_t)min((uint64_t)RS_TILE, (uint64_t)n - tile0);
+    const uint32_t base = warp * (32 * RS_ITEMS);
     uint64_t key[RS_ITEMS];
     uint32_t val[RS_ITEMS], off[RS_ITEMS];
 #pragma unroll
     for (int r = 0; r < RS_ITEMS; ++r) {
-        const uint64_t i = base + (uint64_t)r * 32u + lane;
-        const bool valid = i < n;
+        const uint32_t i = base + r * 32u + lane;
         key[r] = 0; val[r] = 0;
-        if (valid) { key[r] = keys_in[i]; val[r] = vals_in[i]; }
+        if (i < nv) { key[r] = keys_in[tile0 + i]; val[r] = vals_in[tile0 + i]; }
     }
 #pragma unroll
     for (int r = 0; r < RS_ITEMS; ++r) {
-        const bool valid = base + (uint64_t)r * 32u + lane < n;
+        const bool valid = base + r * 32u + lane < nv;
         // invalid lanes get a private pseudo-digit so they only match themselves
         const uint32_t dgt = valid ? ((uint32_t)(key[r] >> shift) & 255u) : (256u + lane);
         const uint32_t peers = __match_any_sync(0xFFFFFFFFu, dgt);
@@ -110,18 +140,43 @@ __global__ void __launch_bounds__(RS_THREADS) rs_scatter_kernel(const uint64_t* 
         __syncwarp();
     }
     __syncthreads();
-    {   // digit tid: warp w's keys of this digit start at tile offset + counts of the warps before it
-        uint32_t run = ghist[(uint64_t)tid * nblocks + blockIdx.x];
+    {   // digit tid: the warps' shares of the digit become offsets inside the digit's run; the runs are laid out by an
+        // exclusive scan of the digit totals over the block
+        uint32_t run = 0;
 #pragma unroll
         for (int w = 0; w < RS_WARPS; ++w) { const uint32_t c = cnt[w][tid]; cnt[w][tid] = run; run += c; }
+        uint32_t inc = run;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+            if (lane >= (uint32_t)o) inc += t;
+        }
+        if (lane == 31u) wsum[warp] = inc;
+        __syncthreads();
+        uint32_t lstart = inc - run;
+        for (uint32_t w = 0; w < warp; ++w) lstart += wsum[w];
+        delta[tid] = ghist[(uint64_t)tid * nblocks + blockIdx.x] - lstart;
+#pragma unroll
+        for (int w = 0; w < RS_WARPS; ++w) cnt[w][tid] += lstart;
     }
     __syncthreads();
 #pragma unroll
     for (int r = 0; r < RS_ITEMS; ++r) {
-        if (base + (uint64_t)r * 32u + lane < n) {
-            const uint32_t pos = cnt[warp][(uint32_t)(key[r] >> shift) & 255u] + off[r];
-            keys_out[pos] = key[r];
-            vals_out[pos] = val[r];
+        if (base + r * 32u + lane < nv) {
+            const uint32_t lp = cnt[warp][(uint32_t)(key[r] >> shift) & 255u] + off[r];
+            skey[lp] = key[r];
+            sval[lp] = val[r];
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < RS_ITEMS; ++r) {
+        const uint32_t i = r * RS_THREADS + tid;
+        if (i < nv) {
+            const uint64_t k = skey[i];
+            const uint32_t pos = i + delta[(uint32_t)(k >> shift) & 255u];
+            keys_out[pos] = k;
+            vals_out[pos] = sval[i];
         }
     }
 }
@@ -581,10 +636,14 @@ int lbvh_build(const float4* d_lo, const float4* d_hi, uint32_t n, cudaStream_t 
     // The levels are queued COLLAPSE_CHUNK at a time with their item counts on the device; the nodes are written
     // straight into the caller's array when it is likely to be large enough (checked afterwards), else into scratch.
     const uint32_t max_nodes = nl;
-    constexpr int COLLAPSE_CHUNK = 16;
+    constexpr int COLLAPSE_MAX_CHUNK = 16;
+    // levels queued per host round trip: an 8-wide tree over nl records is about log8(nl) + 6 levels deep
+    int chunk = 7;
+    for (uint32_t m = nl; m > 1u; m >>= 3) ++chunk;
+    const int COLLAPSE_CHUNK = std::min(chunk, COLLAPSE_MAX_CHUNK);
     CK(qa.alloc(sizeof(uint2) * (size_t)max_nodes));
     CK(qb.alloc(sizeof(uint2) * (size_t)max_nodes));
-    CK(ctr.alloc((COLLAPSE_CHUNK + 2) * sizeof(uint32_t)));  // [0] = node counter, [1..] = items per level of the chunk
+    CK(ctr.alloc((COLLAPSE_MAX_CHUNK + 2) * sizeof(uint32_t)));  // [0] = node counter, [1..] = items per level of the chunk
     BinTree T{left.as<uint32_t>(), right.as<uint32_t>(), first.as<uint32_t>(), last.as<uint32_t>(), blo.as<float4>(), bhi.as<float4>(), nl};
     const uint32_t grid = std::min(cdiv(max_nodes, 128), 148u * 8u);
     uint32_t n_nodes = 0, levels = 0;
@@ -598,7 +657,7 @@ int lbvh_build(const float4* d_lo, const float4* d_hi, uint32_t n, cudaStream_t 
         }
         const uint2 root_item = make_uint2(0u, 0u);
         CK(cudaMemcpyAsync(qa.p, &root_item, sizeof(uint2), cudaMemcpyHostToDevice, stream));
-        uint32_t h_ctr[COLLAPSE_CHUNK + 2] = {1u, 1u};  // one node (the root) allocated, one item at level 0
+        uint32_t h_ctr[COLLAPSE_MAX_CHUNK + 2] = {1u, 1u};  // one node (the root) allocated, one item at level 0
         CK(cudaMemcpyAsync(ctr.p, h_ctr, sizeof(h_ctr), cudaMemcpyHostToDevice, stream));
         uint2* qi = qa.as<uint2>();
         uint2* qo = qb.as<uint2>();
@@ -614,7 +673,7 @@ int lbvh_build(const float4* d_lo, const float4* d_hi, uint32_t n, cudaStream_t 
             for (int l = 0; l < COLLAPSE_CHUNK; ++l) levels += h_ctr[1 + l] != 0u;
             if (h_ctr[1 + COLLAPSE_CHUNK] == 0u) break;
             if (levels > 4096) return (int)cudaErrorUnknown;
-            uint32_t next[COLLAPSE_CHUNK + 2] = {h_ctr[0], h_ctr[1 + COLLAPSE_CHUNK]};
+            uint32_t next[COLLAPSE_MAX_CHUNK + 2] = {h_ctr[0], h_ctr[1 + COLLAPSE_CHUNK]};
             CK(cudaMemcpyAsync(ctr.p, next, sizeof(next), cudaMemcpyHostToDevice, stream));
         }
         n_nodes = h_ctr[0];
