@@ -11,6 +11,8 @@
 #include <algorithm>
 #include <cfloat>
 #include <cstdio>
+#include <cstdlib>
+#include <utility>
 #include <vector>
 
 #include "grt_internal.h"
@@ -345,8 +347,13 @@ __device__ __forceinline__ int delta_fn(const uint64_t* __restrict__ keys, int n
     return __clzll((long long)(a ^ b));
 }
 
-__global__ void karras_kernel(const uint64_t* __restrict__ keys, int n, uint32_t* __restrict__ left, uint32_t* __restrict__ right,
-                              uint32_t* __restrict__ parent, uint32_t* __restrict__ first, uint32_t* __restrict__ last) {
+// A binary node is one 48-byte record (children, leaf range, box): whoever visits a node touches two sectors, not six arrays.
+struct BinNode {
+    uint32_t left, right, first, last;
+    float4 lo, hi;
+};
+
+__global__ void karras_kernel(const uint64_t* __restrict__ keys, int n, BinNode* __restrict__ bn, uint32_t* __restrict__ parent) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n - 1) return;
     const int d = (delta_fn(keys, n, i, i + 1) - delta_fn(keys, n, i, i - 1)) >= 0 ? 1 : -1;
@@ -368,26 +375,23 @@ __global__ void karras_kernel(const uint64_t* __restrict__ keys, int n, uint32_t
     const int lo = min(i, j), hi = max(i, j);
     const uint32_t l_id = (lo == gamma) ? (uint32_t)(n - 1 + gamma) : (uint32_t)gamma;
     const uint32_t r_id = (hi == gamma + 1) ? (uint32_t)(n - 1 + gamma + 1) : (uint32_t)(gamma + 1);
-    left[i] = l_id;
-    right[i] = r_id;
+    *reinterpret_cast<uint4*>(&bn[i]) = make_uint4(l_id, r_id, (uint32_t)lo, (uint32_t)hi);
     parent[l_id] = (uint32_t)i;
     parent[r_id] = (uint32_t)i;
-    first[i] = (uint32_t)lo;
-    last[i] = (uint32_t)hi;
     if (i == 0) parent[0] = 0xFFFFFFFFu;
 }
 
+// leafbox[2j], leafbox[2j+1] = box of the j-th record in Morton order
 __global__ void leaf_boxes_kernel(const float4* __restrict__ lo, const float4* __restrict__ hi, const uint32_t* __restrict__ perm, uint32_t n,
-                                  float4* __restrict__ blo, float4* __restrict__ bhi) {
+                                  float4* __restrict__ leafbox) {
     const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= n) return;
     const uint32_t i = perm[j];
-    blo[n - 1 + j] = lo[i];
-    bhi[n - 1 + j] = hi[i];
+    leafbox[2u * j] = lo[i];
+    leafbox[2u * j + 1u] = hi[i];
 }
 
-__global__ void refit_kernel(uint32_t n, const uint32_t* __restrict__ parent, const uint32_t* __restrict__ left, const uint32_t* __restrict__ right,
-                             float4* blo, float4* bhi, uint32_t* flags) {
+__global__ void refit_kernel(uint32_t n, const uint32_t* __restrict__ parent, BinNode* bn, const float4* __restrict__ leafbox, uint32_t* flags) {
     const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= n) return;
     uint32_t p = parent[n - 1 + j];
@@ -395,21 +399,23 @@ __global__ void refit_kernel(uint32_t n, const uint32_t* __restrict__ parent, co
         __threadfence();
         if (atomicAdd(&flags[p], 1u) == 0u) return;  // first child to arrive: the sibling will finish the job
         __threadfence();
-        const uint32_t l = left[p], r = right[p];
-        const float4 la = __ldcg(&blo[l]), lb = __ldcg(&bhi[l]), ra = __ldcg(&blo[r]), rb = __ldcg(&bhi[r]);
-        __stcg(&blo[p], make_float4(fminf(la.x, ra.x), fminf(la.y, ra.y), fminf(la.z, ra.z), 0.f));
-        __stcg(&bhi[p], make_float4(fmaxf(lb.x, rb.x), fmaxf(lb.y, rb.y), fmaxf(lb.z, rb.z), 0.f));
+        const uint32_t l = bn[p].left, r = bn[p].right;
+        const float4* pl = l >= n - 1 ? leafbox + 2u * (l - (n - 1)) : &bn[l].lo;
+        const float4* pr = r >= n - 1 ? leafbox + 2u * (r - (n - 1)) : &bn[r].lo;
+        const float4 la = __ldcg(pl), lb = __ldcg(pl + 1), ra = __ldcg(pr), rb = __ldcg(pr + 1);
+        __stcg(&bn[p].lo, make_float4(fminf(la.x, ra.x), fminf(la.y, ra.y), fminf(la.z, ra.z), 0.f));
+        __stcg(&bn[p].hi, make_float4(fmaxf(lb.x, rb.x), fmaxf(lb.y, rb.y), fmaxf(lb.z, rb.z), 0.f));
         p = parent[p];
     }
 }
 
 // ------------------------------------------------------------------------------------------- collapse to 8-wide
 struct BinTree {
-    const uint32_t *left, *right, *first, *last;
-    const float4 *blo, *bhi;
+    const BinNode* bn;
+    const float4* leafbox;
     uint32_t n;
-    __device__ __forceinline__ uint32_t count(uint32_t id) const { return id >= n - 1 ? 1u : last[id] - first[id] + 1u; }
-    __device__ __forceinline__ uint32_t start(uint32_t id) const { return id >= n - 1 ? id - (n - 1) : first[id]; }
+    // box of a unified node id (internal i in [0, n-1), leaf j as (n-1)+j): lo at [0], hi at [1]
+    __device__ __forceinline__ const float4* box(uint32_t id) const { return id >= n - 1 ? leafbox + 2u * (id - (n - 1)) : &bn[id].lo; }
 };
 
 __device__ __forceinline__ void write_child(WideNode* nd, int k, float4 lo, float4 hi, uint32_t ref) {
@@ -432,10 +438,11 @@ __device__ __forceinline__ Slot load_slot(const BinTree& T, uint32_t id) {
         s.cnt = 1u; s.first = id - (T.n - 1); s.l = s.r = 0u; s.area = -1.0f;
         return s;
     }
-    const uint32_t f = T.first[id], la = T.last[id];
-    s.l = T.left[id];
-    s.r = T.right[id];
-    const float4 a = T.blo[id], d = T.bhi[id];
+    const uint4 h = *reinterpret_cast<const uint4*>(&T.bn[id]);
+    const float4 a = T.bn[id].lo, d = T.bn[id].hi;
+    const uint32_t f = h.z, la = h.w;
+    s.l = h.x;
+    s.r = h.y;
     const float ex = d.x - a.x, ey = d.y - a.y, ez = d.z - a.z;
     s.area = ex * ey + ey * ez + ez * ex;
     s.cnt = la - f + 1u;
@@ -461,7 +468,7 @@ __global__ void __launch_bounds__(128) collapse_kernel(BinTree T, const uint2* _
         Slot sl[WIDE];
         int ns = 2;
         {
-            const uint32_t l = T.left[b], r = T.right[b];
+            const uint32_t l = T.bn[b].left, r = T.bn[b].right;
             sl[0] = load_slot(T, l);
             sl[1] = load_slot(T, r);
         }
@@ -529,7 +536,7 @@ __global__ void __launch_bounds__(128) collapse_kernel(BinTree T, const uint2* _
                     q_out[qo++] = make_uint2(id, wi);
                     ref = wi++;
                 }
-                if (fits) write_child(nd, k, T.blo[id], T.bhi[id], ref);
+                if (fits) { const float4* bx = T.box(id); write_child(nd, k, bx[0], bx[1], ref); }
             } else if (fits) {
                 write_child(nd, k, make_float4(INFINITY, INFINITY, INFINITY, 0.f), make_float4(-INFINITY, -INFINITY, -INFINITY, 0.f), CHILD_EMPTY);
             }
@@ -551,6 +558,37 @@ __global__ void tiny_root_kernel(const float4* __restrict__ lo, const float4* __
     for (int k = 1; k < WIDE; ++k)
         write_child(&nodes[0], k, make_float4(INFINITY, INFINITY, INFINITY, 0.f), make_float4(-INFINITY, -INFINITY, -INFINITY, 0.f), CHILD_EMPTY);
 }
+
+// GRT_BUILD_TIMING=1: event-timed phases of lbvh_build on stderr (diagnostic; the events themselves cost a few microseconds)
+struct PhaseTimer {
+    bool on = false;
+    cudaStream_t stream = nullptr;
+    std::vector<std::pair<const char*, cudaEvent_t>> marks;
+    explicit PhaseTimer(cudaStream_t s) : stream(s) {
+        const char* e = getenv("GRT_BUILD_TIMING");
+        on = e && e[0] == '1';
+        mark("start");
+    }
+    void mark(const char* name) {
+        if (!on) return;
+        cudaEvent_t ev;
+        cudaEventCreate(&ev);
+        cudaEventRecord(ev, stream);
+        marks.emplace_back(name, ev);
+    }
+    ~PhaseTimer() {
+        if (!on) return;
+        cudaStreamSynchronize(stream);
+        fprintf(stderr, "[lbvh_build]");
+        for (size_t i = 1; i < marks.size(); ++i) {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, marks[i - 1].second, marks[i].second);
+            fprintf(stderr, " %s %.1f us |", marks[i].first, ms * 1e3f);
+        }
+        fprintf(stderr, "\n");
+        for (auto& m : marks) cudaEventDestroy(m.second);
+    }
+};
 
 struct DevBuf {  // a build temporary: from the context's scratch block, else cudaMalloc'd and freed on scope exit
     void* p = nullptr;
@@ -574,6 +612,7 @@ int lbvh_build(const float4* d_lo, const float4* d_hi, uint32_t n, cudaStream_t 
     if (n == 0) return 0;
     if (n >= (1u << 28)) return (int)cudaErrorInvalidValue;
     const int TB = 256;
+    PhaseTimer pt(stream);
     DevBuf bounds, keys, keys2, vals2;
     bounds.scratch = keys.scratch = keys2.scratch = vals2.scratch = scratch;
     CK(bounds.alloc(8 * sizeof(uint32_t)));
@@ -590,12 +629,14 @@ int lbvh_build(const float4* d_lo, const float4* d_hi, uint32_t n, cudaStream_t 
     out->perm = d_perm;
     morton_kernel<<<cdiv(n, TB), TB, 0, stream>>>(d_lo, d_hi, n, bounds.as<uint32_t>(), keys.as<uint64_t>(), d_perm);
     ++*launches;
+    pt.mark("bounds+morton");
     bool in_tmp = false;
     int rc = radix_sort_pairs(keys.as<uint64_t>(), keys2.as<uint64_t>(), d_perm, vals2.as<uint32_t>(), n, stream, launches, &in_tmp, scratch);
     if (rc) return rc;
     uint32_t h_bounds[8];
     CK(cudaMemcpyAsync(h_bounds, bounds.p, sizeof(h_bounds), cudaMemcpyDeviceToHost, stream));
     CK(cudaStreamSynchronize(stream));
+    pt.mark("sort+sync");
     const uint32_t nl = h_bounds[6];
     out->n_live = nl;
     for (int k = 0; k < 3; ++k) { out->lo[k] = dec_f(h_bounds[k]); out->hi[k] = dec_f(h_bounds[3 + k]); }
@@ -613,23 +654,18 @@ int lbvh_build(const float4* d_lo, const float4* d_hi, uint32_t n, cudaStream_t 
         return 0;
     }
 
-    DevBuf left, right, parent, first, last, blo, bhi, flags, qa, qb, ctr, wide_tmp;
-    for (DevBuf* b : {&left, &right, &parent, &first, &last, &blo, &bhi, &flags, &qa, &qb, &ctr, &wide_tmp}) b->scratch = scratch;
-    CK(left.alloc(4ull * (nl - 1)));
-    CK(right.alloc(4ull * (nl - 1)));
-    CK(first.alloc(4ull * (nl - 1)));
-    CK(last.alloc(4ull * (nl - 1)));
+    DevBuf bn, leafbox, parent, flags, qa, qb, ctr, wide_tmp;
+    for (DevBuf* b : {&bn, &leafbox, &parent, &flags, &qa, &qb, &ctr, &wide_tmp}) b->scratch = scratch;
+    CK(bn.alloc(sizeof(BinNode) * (size_t)(nl - 1)));
+    CK(leafbox.alloc(32ull * nl));
     CK(parent.alloc(4ull * (2ull * nl - 1)));
-    CK(blo.alloc(16ull * (2ull * nl - 1)));
-    CK(bhi.alloc(16ull * (2ull * nl - 1)));
     CK(flags.alloc(4ull * (nl - 1)));
     CK(cudaMemsetAsync(flags.p, 0, 4ull * (nl - 1), stream));
-    karras_kernel<<<cdiv(nl - 1, TB), TB, 0, stream>>>(keys.as<uint64_t>(), (int)nl, left.as<uint32_t>(), right.as<uint32_t>(),
-                                                      parent.as<uint32_t>(), first.as<uint32_t>(), last.as<uint32_t>());
-    leaf_boxes_kernel<<<cdiv(nl, TB), TB, 0, stream>>>(d_lo, d_hi, d_perm, nl, blo.as<float4>(), bhi.as<float4>());
-    refit_kernel<<<cdiv(nl, TB), TB, 0, stream>>>(nl, parent.as<uint32_t>(), left.as<uint32_t>(), right.as<uint32_t>(), blo.as<float4>(),
-                                                 bhi.as<float4>(), flags.as<uint32_t>());
+    karras_kernel<<<cdiv(nl - 1, TB), TB, 0, stream>>>(keys.as<uint64_t>(), (int)nl, bn.as<BinNode>(), parent.as<uint32_t>());
+    leaf_boxes_kernel<<<cdiv(nl, TB), TB, 0, stream>>>(d_lo, d_hi, d_perm, nl, leafbox.as<float4>());
+    refit_kernel<<<cdiv(nl, TB), TB, 0, stream>>>(nl, parent.as<uint32_t>(), bn.as<BinNode>(), leafbox.as<float4>(), flags.as<uint32_t>());
     *launches += 3;
+    pt.mark("karras+leaf+refit");
 
     // collapse, level by level.  Upper bound on wide nodes: every wide node but the root is a binary
     // internal node with > LEAF_MAX prims, and two such nodes never share a leaf run, so <= nl.
@@ -644,7 +680,7 @@ int lbvh_build(const float4* d_lo, const float4* d_hi, uint32_t n, cudaStream_t 
     CK(qa.alloc(sizeof(uint2) * (size_t)max_nodes));
     CK(qb.alloc(sizeof(uint2) * (size_t)max_nodes));
     CK(ctr.alloc((COLLAPSE_MAX_CHUNK + 2) * sizeof(uint32_t)));  // [0] = node counter, [1..] = items per level of the chunk
-    BinTree T{left.as<uint32_t>(), right.as<uint32_t>(), first.as<uint32_t>(), last.as<uint32_t>(), blo.as<float4>(), bhi.as<float4>(), nl};
+    BinTree T{bn.as<BinNode>(), leafbox.as<float4>(), nl};
     const uint32_t grid = std::min(cdiv(max_nodes, 128), 148u * 8u);
     uint32_t n_nodes = 0, levels = 0;
     WideNode* target = (reuse_nodes && reuse_cap >= nl / 6u + 16u) ? reuse_nodes : nullptr;
@@ -681,6 +717,7 @@ int lbvh_build(const float4* d_lo, const float4* d_hi, uint32_t n, cudaStream_t 
         target = nullptr;  // the caller's array was too small after all: once more, into scratch
     }
     CK(cudaGetLastError());
+    pt.mark("collapse+sync");
     WideNode* nodes = target;
     if (target != reuse_nodes) {
         nodes = n_nodes <= reuse_cap ? reuse_nodes : nullptr;
