@@ -315,6 +315,13 @@ __device__ __forceinline__ uint64_t expand21(uint64_t x) {
     return x;
 }
 
+// GRT_MORTON_SIZE_EVERY = k > 0: extended Morton code (Vinkler, Bittner, Havran 2017) -- after every k levels of x,y,z bits one
+// bit of the box's diagonal (relative to the scene's) is inserted, so that primitives much larger than their neighbours
+// split off high in the tree instead of inflating the boxes of every node down to their leaf.  0 = plain 63-bit code.
+#ifndef GRT_MORTON_SIZE_EVERY
+#define GRT_MORTON_SIZE_EVERY 0
+#endif
+
 __global__ void morton_kernel(const float4* __restrict__ lo, const float4* __restrict__ hi, uint32_t n, const uint32_t* __restrict__ bounds,
                               uint64_t* __restrict__ keys, uint32_t* __restrict__ vals) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -324,15 +331,33 @@ __global__ void morton_kernel(const float4* __restrict__ lo, const float4* __res
     if (a.x <= b.x) {
         const float c[3] = {0.5f * (a.x + b.x), 0.5f * (a.y + b.y), 0.5f * (a.z + b.z)};
         uint64_t q[3];
+        float ext2 = 0.0f;
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
             const float mn = dec_f(bounds[k]), mx = dec_f(bounds[3 + k]);
             const float ext = fmaxf(mx - mn, 1e-30f);
+            ext2 += ext * ext;
             float u = (c[k] - mn) / ext;
             u = fminf(fmaxf(u, 0.0f), 1.0f);
             q[k] = (uint64_t)min(2097151u, (uint32_t)(u * 2097152.0f));
         }
-        key = (expand21(q[0]) << 2) | (expand21(q[1]) << 1) | expand21(q[2]);
+        if (GRT_MORTON_SIZE_EVERY == 0) {
+            key = (expand21(q[0]) << 2) | (expand21(q[1]) << 1) | expand21(q[2]);
+        } else {
+            const float dx = b.x - a.x, dy = b.y - a.y, dz = b.z - a.z;
+            const float rel = fminf(sqrtf((dx * dx + dy * dy + dz * dz) / ext2), 1.0f);
+            const uint32_t qs = min(2097151u, (uint32_t)(rel * 2097152.0f));
+            key = 0;
+            int bits = 0, lvl = 20, sb = 20;
+            while (bits < 63) {
+                for (int r = 0; r < GRT_MORTON_SIZE_EVERY && bits < 63; ++r, --lvl) {
+#pragma unroll
+                    for (int k = 0; k < 3; ++k)
+                        if (bits < 63) { key = (key << 1) | ((q[k] >> lvl) & 1ull); ++bits; }
+                }
+                if (bits < 63) { key = (key << 1) | ((uint64_t)(qs >> sb) & 1ull); ++bits; --sb; }
+            }
+        }
     }
     keys[i] = key;
     vals[i] = i;

@@ -47,7 +47,9 @@ struct grtContext {
     std::vector<uint2> h_meta;
     std::vector<std::vector<float>> h_normals;  // per mesh, transformed
     std::vector<std::vector<uint32_t>> h_faces; // per mesh
-    std::vector<void*> mesh_allocs;             // per-mesh device arrays
+    std::vector<void*> mesh_allocs;             // mesh device arrays that did not fit into mesh_pool (freed on the next build)
+    BuildScratch mesh_pool;                     // faces / normals / Mesh table / triangle records / header of the current mesh accel
+    uint32_t m_nodes_cap = 0;                   // capacity of m_nodes (kept across rebuilds)
     MeshDev* d_meshes = nullptr;
     WideNode* m_nodes = nullptr;
     TriRec* m_tris = nullptr;
@@ -114,10 +116,10 @@ static int reserve_particles(grtContext* c, uint64_t n) {
     return 0;
 }
 static void free_mesh_accel(grtContext* c) {
-    cudaFree(c->m_nodes); cudaFree(c->m_tris); cudaFree(c->d_m_header); cudaFree(c->d_meshes);
+    // the arrays live in mesh_pool (or in mesh_allocs when the pool was too small); the node array is kept for the next build
     for (void* p : c->mesh_allocs) cudaFree(p);
     c->mesh_allocs.clear();
-    c->m_nodes = nullptr; c->m_tris = nullptr; c->d_m_header = nullptr; c->d_meshes = nullptr;
+    c->m_tris = nullptr; c->d_m_header = nullptr; c->d_meshes = nullptr;
     c->m_count = c->m_nnodes = 0;
 }
 
@@ -155,6 +157,8 @@ int grtDestroy(grtContext* c) {
     free_mesh_accel(c);
     cudaFree(c->d_particles); cudaFree(c->d_s); cudaFree(c->d_counters); cudaFree(c->d_tile_counter); cudaFree(c->d_frame);
     c->scratch.release();
+    c->mesh_pool.release();
+    cudaFree(c->m_nodes);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     if (c->ev_b0) cudaEventDestroy(c->ev_b0);
     if (c->ev_b1) cudaEventDestroy(c->ev_b1);
@@ -505,58 +509,83 @@ int grtBuildMeshAccel(grtContext* c, void* stream_v, uint64_t* mesh_handle_out, 
     const uint32_t nm = (uint32_t)c->h_faces.size();
     const uint32_t nt = (uint32_t)c->h_meta.size();
     if (nm == 0) return 0;
+    // Moving a primitive rebuilds this accel every frame (updateInstanceTransforms, src/GaussianTracer.cpp:711-794): the
+    // persistent arrays come from a pool that is kept between builds, the temporaries from the build scratch block.
+    c->mesh_pool.begin();
+    auto palloc = [&](size_t bytes, void** out) -> cudaError_t {
+        *out = c->mesh_pool.get(bytes ? bytes : 4);
+        if (*out) return cudaSuccess;
+        cudaError_t e = cudaMalloc(out, bytes ? bytes : 4);
+        if (e == cudaSuccess) c->mesh_allocs.push_back(*out);
+        return e;
+    };
     // Mesh{faces, vertex_normals}[] exactly as sendGeometryAttributesToDevice builds it (src/GaussianTracer.cpp:653-709)
     std::vector<MeshDev> hm(nm);
     for (uint32_t m = 0; m < nm; ++m) {
         void *df = nullptr, *dn = nullptr;
-        CU(c, cudaMalloc(&df, std::max<size_t>(4, c->h_faces[m].size() * 4)));
-        c->mesh_allocs.push_back(df);
-        CU(c, cudaMalloc(&dn, std::max<size_t>(4, c->h_normals[m].size() * 4)));
-        c->mesh_allocs.push_back(dn);
+        CU(c, palloc(c->h_faces[m].size() * 4, &df));
+        CU(c, palloc(c->h_normals[m].size() * 4, &dn));
         CU(c, cudaMemcpyAsync(df, c->h_faces[m].data(), c->h_faces[m].size() * 4, cudaMemcpyHostToDevice, stream));
         CU(c, cudaMemcpyAsync(dn, c->h_normals[m].data(), c->h_normals[m].size() * 4, cudaMemcpyHostToDevice, stream));
         hm[m].faces = (uint3*)df;
         hm[m].vertex_normals = (float3*)dn;
     }
-    CU(c, cudaMalloc(&c->d_meshes, sizeof(MeshDev) * nm));
+    { void* p = nullptr; CU(c, palloc(sizeof(MeshDev) * nm, &p)); c->d_meshes = (MeshDev*)p; }
     CU(c, cudaMemcpyAsync(c->d_meshes, hm.data(), sizeof(MeshDev) * nm, cudaMemcpyHostToDevice, stream));
     if (d_meshes_out) *d_meshes_out = c->d_meshes;
     if (nt == 0) { CU(c, cudaStreamSynchronize(stream)); return 0; }
-    cudaEvent_t e0, e1;
-    CU(c, cudaEventCreate(&e0));
-    CU(c, cudaEventCreate(&e1));
-    CU(c, cudaEventRecord(e0, stream));
-    float* d_tri9 = nullptr; uint2* d_meta = nullptr; float4 *d_lo = nullptr, *d_hi = nullptr;
-    CU(c, cudaMalloc(&d_tri9, sizeof(float) * 9ull * nt));
-    CU(c, cudaMalloc(&d_meta, sizeof(uint2) * (size_t)nt));
-    CU(c, cudaMalloc(&d_lo, sizeof(float4) * (size_t)nt));
-    CU(c, cudaMalloc(&d_hi, sizeof(float4) * (size_t)nt));
+    if (!c->ev_b0) { CU(c, cudaEventCreate(&c->ev_b0)); CU(c, cudaEventCreate(&c->ev_b1)); }
+    CU(c, cudaEventRecord(c->ev_b0, stream));
+    c->scratch.begin();
+    struct Tmp {  // scratch block, else cudaMalloc'd for this build only
+        void* p = nullptr; bool owned = false;
+        ~Tmp() { if (owned) cudaFree(p); }
+        cudaError_t alloc(BuildScratch& s, size_t bytes) {
+            p = s.get(bytes);
+            if (p) return cudaSuccess;
+            owned = true;
+            return cudaMalloc(&p, bytes);
+        }
+    } t_tri9, t_meta, t_lo, t_hi;
+    CU(c, t_tri9.alloc(c->scratch, sizeof(float) * 9ull * nt));
+    CU(c, t_meta.alloc(c->scratch, sizeof(uint2) * (size_t)nt));
+    CU(c, t_lo.alloc(c->scratch, sizeof(float4) * (size_t)nt));
+    CU(c, t_hi.alloc(c->scratch, sizeof(float4) * (size_t)nt));
+    float* d_tri9 = (float*)t_tri9.p; uint2* d_meta = (uint2*)t_meta.p; float4 *d_lo = (float4*)t_lo.p, *d_hi = (float4*)t_hi.p;
     CU(c, cudaMemcpyAsync(d_tri9, c->h_tri9.data(), sizeof(float) * 9ull * nt, cudaMemcpyHostToDevice, stream));
     CU(c, cudaMemcpyAsync(d_meta, c->h_meta.data(), sizeof(uint2) * (size_t)nt, cudaMemcpyHostToDevice, stream));
     int rc = mesh_compute_boxes(d_tri9, nt, d_lo, d_hi, stream, &c->launches);
     LbvhResult res;
-    c->scratch.begin();
+    res.reuse_nodes = c->m_nodes;
+    res.reuse_cap = c->m_nodes_cap;
     if (!rc) rc = lbvh_build(d_lo, d_hi, nt, stream, &res, &c->launches, &c->scratch);
     if (!rc && res.n_live) {
-        rc = (int)cudaMalloc(&c->m_tris, sizeof(TriRec) * (size_t)res.n_live);
+        void* p = nullptr;
+        rc = (int)palloc(sizeof(TriRec) * (size_t)res.n_live, &p);
+        c->m_tris = (TriRec*)p;
         if (!rc) rc = mesh_gather(d_tri9, d_meta, res.perm, res.n_live, c->m_tris, stream, &c->launches);
     }
     cudaError_t es = cudaStreamSynchronize(stream);
-    cudaFree(d_tri9); cudaFree(d_meta); cudaFree(d_lo); cudaFree(d_hi);
     if (res.perm_owned) cudaFree(res.perm);
-    if (rc || es != cudaSuccess) { cudaFree(res.nodes); return fail(c, "mesh accel build failed: %s", cudaGetErrorString(rc ? (cudaError_t)rc : es)); }
-    c->m_nodes = res.nodes; c->m_count = res.n_live; c->m_nnodes = res.n_nodes;
+    if (res.nodes && res.nodes != c->m_nodes) {
+        cudaFree(c->m_nodes);
+        c->m_nodes = res.nodes;
+        c->m_nodes_cap = res.nodes_cap ? res.nodes_cap : res.n_nodes;
+    }
+    if (rc || es != cudaSuccess) { free_mesh_accel(c); return fail(c, "mesh accel build failed: %s", cudaGetErrorString(rc ? (cudaError_t)rc : es)); }
+    c->m_count = res.n_live; c->m_nnodes = res.n_nodes;
     if (res.n_live) {
         AccelHeader h{};
         h.magic = ACCEL_MAGIC_MESH; h.nodes = c->m_nodes; h.tris = c->m_tris; h.n_prims = res.n_live; h.n_nodes = res.n_nodes;
-        CU(c, cudaMalloc(&c->d_m_header, sizeof(AccelHeader)));
+        void* p = nullptr;
+        CU(c, palloc(sizeof(AccelHeader), &p));
+        c->d_m_header = (AccelHeader*)p;
         CU(c, cudaMemcpyAsync(c->d_m_header, &h, sizeof(h), cudaMemcpyHostToDevice, stream));
     }
-    CU(c, cudaEventRecord(e1, stream));
+    CU(c, cudaEventRecord(c->ev_b1, stream));
     CU(c, cudaStreamSynchronize(stream));
     float ms = 0;
-    cudaEventElapsedTime(&ms, e0, e1);
-    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaEventElapsedTime(&ms, c->ev_b0, c->ev_b1);
     c->info.n_mesh_triangles = res.n_live; c->info.n_mesh_wide_nodes = res.n_nodes; c->info.mesh_build_ms = ms;
     if (mesh_handle_out) *mesh_handle_out = (uint64_t)(uintptr_t)c->d_m_header;
     return 0;
