@@ -219,7 +219,7 @@ def main():
         k_ms = float(np.mean(kernel_ms))
         achieved = rays * bytes_per_ray / (k_ms * 1e-3) / 1e9
         traffic = None  # dram__bytes_read.sum + dram__bytes_write.sum of trace_kernel from the committed ncu capture
-        ncu_path = os.path.join(ROOT, "profiles", "r1_v9_trace_kernel_ncu.json")
+        ncu_path = os.path.join(ROOT, "profiles", "r1_v12_trace_kernel_ncu.json")
         if os.path.exists(ncu_path) and not args.fisheye:
             traffic = json.load(open(ncu_path)).get("dram_bytes_per_launch")
         line = {
