@@ -13,7 +13,9 @@ def test_rebuild_sequence_matches_fresh_context(grt, ctx):
     W, H = 160, 96
     frames = {}
     # grow, shrink, grow again, empty, and back: every build reuses or regrows the arrays of the one before
-    for n, seed in [(20_000, 5), (60_000, 6), (3_000, 7), (60_000, 6), (0, 8), (20_000, 5)]:
+    # (24 000 after 20 000: the kept node array passes the builder's size guess but is too small in the end, so the collapse
+    # is repeated into scratch -- csrc/build.cu, second attempt)
+    for n, seed in [(20_000, 5), (24_000, 11), (60_000, 6), (3_000, 7), (60_000, 6), (0, 8), (20_000, 5)]:
         if n == 0:
             ctx.set_particles(np.zeros((0, 59), np.float32), 0.01)
             handle, _ = ctx.build_particle_accel()
