@@ -140,7 +140,7 @@ int grtCreate(int device, grtContext** ctx_out) {
     grtContext* c = new grtContext();
     c->device = device;
     c->sm_count = prop.multiProcessorCount;
-    if (cudaMalloc(&c->d_tile_counter, sizeof(uint32_t)) != cudaSuccess || cudaMalloc(&c->d_counters, sizeof(DeviceCounters)) != cudaSuccess || cudaMemset(c->d_counters, 0, sizeof(DeviceCounters)) != cudaSuccess ||
+    if (cudaMalloc(&c->d_tile_counter, 256 * sizeof(uint32_t)) != cudaSuccess || cudaMalloc(&c->d_counters, sizeof(DeviceCounters)) != cudaSuccess || cudaMemset(c->d_counters, 0, sizeof(DeviceCounters)) != cudaSuccess ||
         cudaStreamCreate(&c->own_stream) != cudaSuccess || cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess) {
         delete c;
         return fail(nullptr, "grtCreate: device allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
@@ -613,7 +613,7 @@ static int do_launch(grtContext* c, cudaStream_t stream, const grtParams* p, uin
     ex.tx0 = c->tx0; ex.ty0 = c->ty0; ex.tw = c->tw; ex.th = c->th; ex.trace_max = c->trace_max;
     ex.counters = c->d_counters;
     ex.tile_counter = c->d_tile_counter;
-    CU(c, cudaMemsetAsync(c->d_tile_counter, 0, sizeof(uint32_t), stream));
+    CU(c, cudaMemsetAsync(c->d_tile_counter, 0, 256 * sizeof(uint32_t), stream));  // (one counter per SM in the GRT_SM_REGIONS build)
     CU(c, cudaEventRecord(c->ev0, stream));
     RC(c, launch_trace(*p, ex, c->counters_on, stream, c->sm_count));
     CU(c, cudaEventRecord(c->ev1, stream));
