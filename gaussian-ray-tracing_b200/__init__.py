@@ -98,6 +98,7 @@ GRT_SYMBOLS = [
     "grtEnableCounters", "grtGetCounters", "grtGetBuildInfo", "grtValidateAccel", "grtLastLaunchMs", "grtMalloc",
     "grtFree", "grtMallocHost", "grtFreeHost", "grtMemcpyDtoH", "grtMemcpyHtoD", "grtMemset", "grtStreamCreate",
     "grtStreamDestroy", "grtStreamSynchronize", "grtDebugRadixSort", "grtSetParticlesRaw", "grtLoadPly", "grtGetParticles",
+    "grtLaunchRows", "grtGetAbiLayout",
 ]
 
 _lib = None

@@ -62,7 +62,9 @@ struct grtContext {
     uint32_t tx0 = 0, ty0 = 0, tw = 0, th = 0, trace_max = 0;
     bool counters_on = false;
     DeviceCounters* d_counters = nullptr;
-    uint32_t* d_tile_counter = nullptr;
+    uint32_t* d_tile_counter = nullptr;  // TILE_RING x TILE_SLOT_WORDS: one scheduler counter block per launch in flight
+    uint32_t tile_seq = 0;
+    bool smem_attr_set = false;          // cudaFuncAttributeMaxDynamicSharedMemorySize is per DEVICE: kept per context, not per process
     BuildScratch scratch;  // builder temporaries, kept between builds
     int sm_count = 0;
     // e2e frame
@@ -91,6 +93,13 @@ static int fail(grtContext* ctx, const char* fmt, ...) {
         cudaError_t e_ = (call);                                                                   \
         if (e_ != cudaSuccess) return fail(ctx, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
     } while (0)
+#define DEV(ctx) CU(ctx, cudaSetDevice((ctx)->device))  /* a context is bound to one GPU; the caller's current device may be another */
+constexpr uint32_t TILE_RING = 64, TILE_SLOT_WORDS = 256;
+#ifdef GRT_SM_REGIONS
+#define GRT_SM_REGIONS_HOST GRT_SM_REGIONS
+#else
+#define GRT_SM_REGIONS_HOST 0
+#endif
 #define RC(ctx, call)                                                                                            \
     do {                                                                                                         \
         int r_ = (call);                                                                                         \
@@ -140,7 +149,7 @@ int grtCreate(int device, grtContext** ctx_out) {
     grtContext* c = new grtContext();
     c->device = device;
     c->sm_count = prop.multiProcessorCount;
-    if (cudaMalloc(&c->d_tile_counter, 256 * sizeof(uint32_t)) != cudaSuccess || cudaMalloc(&c->d_counters, sizeof(DeviceCounters)) != cudaSuccess || cudaMemset(c->d_counters, 0, sizeof(DeviceCounters)) != cudaSuccess ||
+    if (cudaMalloc(&c->d_tile_counter, TILE_RING * TILE_SLOT_WORDS * sizeof(uint32_t)) != cudaSuccess || cudaMalloc(&c->d_counters, sizeof(DeviceCounters)) != cudaSuccess || cudaMemset(c->d_counters, 0, sizeof(DeviceCounters)) != cudaSuccess ||
         cudaStreamCreate(&c->own_stream) != cudaSuccess || cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess) {
         delete c;
         return fail(nullptr, "grtCreate: device allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
@@ -177,39 +186,44 @@ int grtMalloc(grtContext* c, size_t bytes, void** out) {
     CU(c, cudaMalloc(out, bytes ? bytes : 1));
     return 0;
 }
-int grtFree(grtContext* c, void* p) { if (!c) return 1; CU(c, cudaFree(p)); return 0; }
+int grtFree(grtContext* c, void* p) { if (!c) return 1; DEV(c); CU(c, cudaFree(p)); return 0; }
 int grtMallocHost(grtContext* c, size_t bytes, void** out) {
     if (!c || !out) return fail(c, "grtMallocHost: bad argument");
+    DEV(c);
     CU(c, cudaMallocHost(out, bytes ? bytes : 1));
     return 0;
 }
-int grtFreeHost(grtContext* c, void* p) { if (!c) return 1; CU(c, cudaFreeHost(p)); return 0; }
+int grtFreeHost(grtContext* c, void* p) { if (!c) return 1; DEV(c); CU(c, cudaFreeHost(p)); return 0; }
 int grtMemcpyDtoH(grtContext* c, void* dst, const void* src, size_t bytes, void* stream) {
     if (!c) return 1;
+    DEV(c);
     CU(c, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     CU(c, cudaStreamSynchronize((cudaStream_t)stream));
     return 0;
 }
 int grtMemcpyHtoD(grtContext* c, void* dst, const void* src, size_t bytes, void* stream) {
     if (!c) return 1;
+    DEV(c);
     CU(c, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
     CU(c, cudaStreamSynchronize((cudaStream_t)stream));
     return 0;
 }
 int grtMemset(grtContext* c, void* p, int value, size_t bytes, void* stream) {
     if (!c) return 1;
+    DEV(c);
     CU(c, cudaMemsetAsync(p, value, bytes, (cudaStream_t)stream));
     return 0;
 }
 int grtStreamCreate(grtContext* c, void** out) {
     if (!c || !out) return 1;
     cudaStream_t s;
+    DEV(c);
     CU(c, cudaStreamCreate(&s));
     *out = (void*)s;
     return 0;
 }
-int grtStreamDestroy(grtContext* c, void* s) { if (!c) return 1; CU(c, cudaStreamDestroy((cudaStream_t)s)); return 0; }
-int grtStreamSynchronize(grtContext* c, void* s) { if (!c) return 1; CU(c, cudaStreamSynchronize((cudaStream_t)s)); return 0; }
+int grtStreamDestroy(grtContext* c, void* s) { if (!c) return 1; DEV(c); CU(c, cudaStreamDestroy((cudaStream_t)s)); return 0; }
+int grtStreamSynchronize(grtContext* c, void* s) { if (!c) return 1; DEV(c); CU(c, cudaStreamSynchronize((cudaStream_t)s)); return 0; }
 
 // ---------------------------------------------------------------- particles
 int grtSetParticles(grtContext* c, const void* host_particles, uint64_t n, float alpha_min) {
@@ -387,6 +401,7 @@ int grtGetParticles(grtContext* c, void* host_out236, uint64_t n) {
     if (!c) return 1;
     if (n > c->n_particles) return fail(c, "grtGetParticles: %llu requested, %llu resident", (unsigned long long)n, (unsigned long long)c->n_particles);
     if (n && !host_out236) return fail(c, "grtGetParticles: host buffer is NULL");
+    DEV(c);
     if (n) CU(c, cudaMemcpy(host_out236, c->d_particles, n * 236ull, cudaMemcpyDeviceToHost));
     return 0;
 }
@@ -399,6 +414,7 @@ int grtBuildParticleAccel(grtContext* c, void* stream_v, uint64_t* handle_out, v
     // arrays of the previous accel when they are large enough and takes its temporaries from the context's scratch block.
     c->p_valid = false;
     c->p_live = c->p_nnodes = c->p_levels = 0;
+    if (c->ev_valid) CU(c, cudaStreamWaitEvent(stream, c->ev1, 0));  // the node / record arrays are reused: wait for the last launch that read them
     if (handle_out) *handle_out = 0;
     if (d_particles_out) *d_particles_out = c->d_particles;
     c->info.n_particles = c->n_particles;
@@ -501,7 +517,9 @@ int grtBuildMeshAccel(grtContext* c, void* stream_v, uint64_t* mesh_handle_out, 
     if (!c) return 1;
     cudaStream_t stream = (cudaStream_t)stream_v;
     CU(c, cudaSetDevice(c->device));
-    CU(c, cudaDeviceSynchronize());  // frames in flight may still read the old mesh arrays
+    // frames in flight may still read the old mesh arrays: the rebuild is ordered behind the context's last launch on the
+    // device (no host-side cudaDeviceSynchronize)
+    if (c->ev_valid) CU(c, cudaStreamWaitEvent(stream, c->ev1, 0));
     free_mesh_accel(c);
     if (mesh_handle_out) *mesh_handle_out = 0;
     if (d_meshes_out) *d_meshes_out = nullptr;
@@ -592,8 +610,10 @@ int grtBuildMeshAccel(grtContext* c, void* stream_v, uint64_t* mesh_handle_out, 
 }
 
 // ---------------------------------------------------------------- render
-static int do_launch(grtContext* c, cudaStream_t stream, const grtParams* p, uint32_t x0, uint32_t y0, uint32_t w, uint32_t h) {
+static int do_launch(grtContext* c, cudaStream_t stream, const grtParams* p, uint32_t x0, uint32_t y0, uint32_t w, uint32_t h,
+                     uint32_t band_rows = 0, uint32_t band_stride = 1, uint32_t band_offset = 0) {
     if (!p) return fail(c, "grtLaunch: host_params is NULL");
+    DEV(c);
     if (p->width == 0 || p->height == 0) return 0;
     if (x0 + w > p->width || y0 + h > p->height) return fail(c, "grtLaunch: tile (%u,%u,%u,%u) outside %ux%u", x0, y0, w, h, p->width, p->height);
     if (p->sh_degree_max > 3) return fail(c, "grtLaunch: sh_degree_max %u > 3", p->sh_degree_max);
@@ -612,10 +632,19 @@ static int do_launch(grtContext* c, cudaStream_t stream, const grtParams* p, uin
     ex.trace_ids = c->dbg_trace_ids; ex.trace_counts = c->dbg_trace_counts;
     ex.tx0 = c->tx0; ex.ty0 = c->ty0; ex.tw = c->tw; ex.th = c->th; ex.trace_max = c->trace_max;
     ex.counters = c->d_counters;
-    ex.tile_counter = c->d_tile_counter;
-    CU(c, cudaMemsetAsync(c->d_tile_counter, 0, 256 * sizeof(uint32_t), stream));  // (one counter per SM in the GRT_SM_REGIONS build)
+    if (band_stride > 1u) {
+        if (band_rows == 0u || (band_rows & 7u)) return fail(c, "grtLaunchRows: band_rows %u must be a positive multiple of 8 (the packet grid)", band_rows);
+        if (band_offset >= band_stride) return fail(c, "grtLaunchRows: band_offset %u >= band_stride %u", band_offset, band_stride);
+        ex.band_groups = band_rows / 8u; ex.band_stride = band_stride; ex.band_offset = band_offset;
+    } else {
+        ex.band_groups = 1u; ex.band_stride = 1u; ex.band_offset = 0u;
+    }
+    // Every launch gets its own block of scheduler counters out of a ring: launches of one context that are in flight on
+    // different streams (tiles or cameras overlapped on one GPU) must not share a tile counter.
+    ex.tile_counter = c->d_tile_counter + (size_t)(c->tile_seq++ % TILE_RING) * TILE_SLOT_WORDS;
+    CU(c, cudaMemsetAsync(ex.tile_counter, 0, (GRT_SM_REGIONS_HOST ? TILE_SLOT_WORDS : 1u) * sizeof(uint32_t), stream));
     CU(c, cudaEventRecord(c->ev0, stream));
-    RC(c, launch_trace(*p, ex, c->counters_on, stream, c->sm_count));
+    RC(c, launch_trace(*p, ex, c->counters_on, stream, c->sm_count, &c->smem_attr_set));
     CU(c, cudaEventRecord(c->ev1, stream));
     c->ev_valid = true;
     c->launches += 1;
@@ -630,6 +659,12 @@ int grtLaunch(grtContext* c, void* stream, const grtParams* p) {
 int grtLaunchTile(grtContext* c, void* stream, const grtParams* p, uint32_t x0, uint32_t y0, uint32_t w, uint32_t h) {
     if (!c) return 1;
     return do_launch(c, (cudaStream_t)stream, p, x0, y0, w, h);
+}
+int grtLaunchRows(grtContext* c, void* stream, const grtParams* p, uint32_t band_rows, uint32_t band_stride, uint32_t band_offset) {
+    if (!c) return 1;
+    if (!p) return fail(c, "grtLaunchRows: host_params is NULL");
+    if (band_stride == 0u) return fail(c, "grtLaunchRows: band_stride is 0");
+    return do_launch(c, (cudaStream_t)stream, p, 0, 0, p->width, p->height, band_rows, band_stride, band_offset);
 }
 int grtLaunchBatch(grtContext* c, void* stream, const grtParams* arr, uint32_t n) {
     if (!c) return 1;
@@ -646,6 +681,7 @@ int grtRenderHost(grtContext* c, const grtParams* p, uint8_t* host_rgb8, uint32_
     if (!p || !host_rgb8) return fail(c, "grtRenderHost: bad argument");
     if (h == 0) { y0 = 0; h = p->height; }
     if (y0 + h > p->height) return fail(c, "grtRenderHost: rows [%u,%u) outside height %u", y0, y0 + h, p->height);
+    DEV(c);
     const size_t need = (size_t)p->width * p->height * 3;
     if (need > c->frame_bytes) {
         cudaFree(c->d_frame);
@@ -674,9 +710,26 @@ int grtSetDebugOutputs(grtContext* c, float* d_rgb32f, uint32_t* d_trace_ids, ui
     c->tx0 = tx0; c->ty0 = ty0; c->tw = tw; c->th = th; c->trace_max = trace_max;
     return 0;
 }
+int grtGetAbiLayout(uint64_t out[32]) {
+    if (!out) return 1;
+    int k = 0;
+    out[k++] = sizeof(grtParams);
+    out[k++] = offsetof(grtParams, output_buffer); out[k++] = offsetof(grtParams, width); out[k++] = offsetof(grtParams, height);
+    out[k++] = offsetof(grtParams, sh_degree_max); out[k++] = offsetof(grtParams, eye); out[k++] = offsetof(grtParams, U);
+    out[k++] = offsetof(grtParams, V); out[k++] = offsetof(grtParams, W); out[k++] = offsetof(grtParams, t_min);
+    out[k++] = offsetof(grtParams, t_max); out[k++] = offsetof(grtParams, minTransmittance); out[k++] = offsetof(grtParams, alpha_min);
+    out[k++] = offsetof(grtParams, handle); out[k++] = offsetof(grtParams, d_particles); out[k++] = offsetof(grtParams, mesh_handle);
+    out[k++] = offsetof(grtParams, mode_fisheye); out[k++] = offsetof(grtParams, d_meshes); out[k++] = offsetof(grtParams, type);
+    out[k++] = offsetof(grtParams, traceState);
+    out[k++] = 236;                 // bytes per particle record the library reads (GaussianParticle, src/GaussianData.h:12-20)
+    out[k++] = sizeof(MeshDev);     // Mesh{faces, vertex_normals} (src/Parameters.h:36-40)
+    while (k < 32) out[k++] = 0;
+    return 0;
+}
 int grtEnableCounters(grtContext* c, int enable) { if (!c) return 1; c->counters_on = enable != 0; return 0; }
 int grtGetCounters(grtContext* c, grtCounters* out, int reset) {
     if (!c || !out) return 1;
+    DEV(c);
     CU(c, cudaDeviceSynchronize());
     DeviceCounters d;
     CU(c, cudaMemcpy(&d, c->d_counters, sizeof(d), cudaMemcpyDeviceToHost));
@@ -693,6 +746,7 @@ int grtGetBuildInfo(grtContext* c, grtBuildInfo* out) { if (!c || !out) return 1
 int grtLastLaunchMs(grtContext* c, float* ms) {
     if (!c || !ms) return 1;
     if (!c->ev_valid) return fail(c, "grtLastLaunchMs: nothing launched yet");
+    DEV(c);
     CU(c, cudaEventSynchronize(c->ev1));
     CU(c, cudaEventElapsedTime(ms, c->ev0, c->ev1));
     return 0;
@@ -703,6 +757,7 @@ int grtValidateAccel(grtContext* c, int which) {
     const WideNode* dn = which ? c->m_nodes : c->p_nodes;
     const uint32_t nn = which ? c->m_nnodes : c->p_nnodes, np = which ? c->m_count : c->p_live;
     if (nn == 0) return np == 0 ? 0 : fail(c, "validate: %u prims but no nodes", np);
+    DEV(c);
     CU(c, cudaDeviceSynchronize());
     std::vector<WideNode> nodes(nn);
     CU(c, cudaMemcpy(nodes.data(), dn, sizeof(WideNode) * (size_t)nn, cudaMemcpyDeviceToHost));

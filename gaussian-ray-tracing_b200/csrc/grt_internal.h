@@ -83,6 +83,9 @@ struct LaunchExtras {
     uint32_t tx0, ty0, tw, th, trace_max;
     DeviceCounters* counters;
     uint32_t* tile_counter;  // persistent-warp scheduler: next 8x4 tile to hand out (zeroed before the launch)
+    // row-band partition of one frame over several GPUs: bands of band_groups 8-row groups; this launch owns the bands b with
+    // b % band_stride == band_offset (band_stride <= 1: the whole rectangle)
+    uint32_t band_groups, band_stride, band_offset;
 };
 
 // ---- generic LBVH builder (build.cu) ----
@@ -135,6 +138,6 @@ int mesh_gather(const float* d_tri9, const uint2* d_meta, const uint32_t* d_perm
                 cudaStream_t stream, unsigned long long* launches);
 
 // trace kernel (trace.cu)
-int launch_trace(const grtParams& p, const LaunchExtras& ex, bool counters, cudaStream_t stream, int sm_count);
+int launch_trace(const grtParams& p, const LaunchExtras& ex, bool counters, cudaStream_t stream, int sm_count, bool* smem_attr_set);
 
 }  // namespace grt

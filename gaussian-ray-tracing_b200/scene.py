@@ -217,6 +217,15 @@ def compose(*glm_mats):
     return M.T.copy()
 
 
+def primitive_position(eye, lookat):
+    """Where createPlane / createSphere put a new primitive: 0.75 eye + 0.25 lookat (src/GaussianTracer.cpp:580-588), in the
+    reference's order of operations."""
+    eye, lookat = _f32(eye), _f32(lookat)
+    cw = np.float32(0.75)
+    gw = np.float32(1.0) - cw
+    return (lookat * gw + eye * cw).astype(np.float32)
+
+
 def create_plane(position):
     """Primitives::createPlane (src/geometry/Primitives.cpp:6-61): 0.3 x 0.5 quad, normal +z, 2 triangles."""
     w, h = np.float32(0.3), np.float32(0.5)

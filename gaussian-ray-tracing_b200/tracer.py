@@ -131,10 +131,7 @@ class GaussianTracer:
     def getPrimitives(self): return self.primitives
 
     def _primitive_position(self):                  # GaussianTracer.cpp:580-588
-        eye = np.array(list(self.params.eye), np.float32)
-        cw = np.float32(0.75)
-        gw = np.float32(1.0) - cw
-        return (self.current_lookat * gw + eye * cw).astype(np.float32)
+        return _scene.primitive_position(np.array(list(self.params.eye), np.float32), self.current_lookat)
 
     def _rebuild_meshes(self):
         self.ctx.set_meshes(self.primitives)

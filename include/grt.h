@@ -133,6 +133,11 @@ int grtBuildMeshAccel(grtContext* ctx, void* stream, uint64_t* mesh_handle_out, 
 int grtLaunch(grtContext* ctx, void* stream, const grtParams* host_params);
 /* Only the pixel rectangle [x0,x0+w) x [y0,y0+h) of the frame is traced (multi-GPU tile partition). */
 int grtLaunchTile(grtContext* ctx, void* stream, const grtParams* host_params, uint32_t x0, uint32_t y0, uint32_t w, uint32_t h);
+/* One frame split over several GPUs in ONE launch per GPU: the frame's rows are cut into bands of band_rows rows (a multiple of
+ * 8, the packet grid) and this launch traces the bands b with b % band_stride == band_offset (rank r of G: stride G, offset r).
+ * The union over the offsets 0..band_stride-1 is bit-identical to grtLaunch's frame.  (SURVEY 8e "Partitioning"; the reference is
+ * single-GPU, src/GaussianTracer.h:50.) */
+int grtLaunchRows(grtContext* ctx, void* stream, const grtParams* host_params, uint32_t band_rows, uint32_t band_stride, uint32_t band_offset);
 /* n cameras, one full frame each (output_buffer per entry). */
 int grtLaunchBatch(grtContext* ctx, void* stream, const grtParams* host_params_array, uint32_t n);
 /* End-to-end convenience with HOST output: traces rows [y0,y0+h) into a context-owned device frame,
@@ -146,6 +151,11 @@ int grtRenderHost(grtContext* ctx, const grtParams* host_params, uint8_t* host_r
  * pixel go to d_trace_ids[((y-ty0)*tw+(x-tx0))*trace_max + k], the total count to d_trace_counts[...]. */
 int grtSetDebugOutputs(grtContext* ctx, float* d_rgb32f, uint32_t* d_trace_ids, uint32_t* d_trace_counts,
                        uint32_t tx0, uint32_t ty0, uint32_t tw, uint32_t th, uint32_t trace_max);
+/* sizeof / offsetof of grtParams as compiled into this library, in the order sizeof, output_buffer, width, height, sh_degree_max, eye,
+ * U, V, W, t_min, t_max, minTransmittance, alpha_min, handle, d_particles, mesh_handle, mode_fisheye, d_meshes, type, traceState,
+ * then the particle record size (236) and sizeof(Mesh).  tests/test_ref_pins.py compares them with the numbers the REFERENCE's own
+ * src/Parameters.h gives (oracle/_ref).  Needs no GPU. */
+int grtGetAbiLayout(uint64_t out32[32]);
 int grtEnableCounters(grtContext* ctx, int enable); /* selects the counting kernel variant */
 int grtGetCounters(grtContext* ctx, grtCounters* out, int reset);
 int grtGetBuildInfo(grtContext* ctx, grtBuildInfo* out);

@@ -869,4 +869,75 @@ void orc_transform_mesh(const float* verts, const float* normals, uint32_t n, co
     }
 }
 
+// ---- batch forms of the known-answer hooks (tests/test_ref_pins.py compares them with the reference-compiled functions of
+// oracle/_ref on 1e5 random inputs each)
+void orc_compute_response_batch(const OrcParticle* ps, uint64_t n, const uint32_t* pidx, const float* o, const float* d, float* out) {
+    for (uint64_t i = 0; i < n; ++i) out[i] = computeResponse(ps[pidx[i]], ld3(o + 3 * i), ld3(d + 3 * i));
+}
+void orc_sh_radiance_batch(const OrcParticle* ps, uint64_t n, const uint32_t* pidx, const float* d, uint32_t deg, int normalise, float* out) {
+    for (uint64_t i = 0; i < n; ++i) {
+        f3 dir = ld3(d + 3 * i);
+        if (normalise) dir = normalize(dir);  // tracer.cuh:262
+        const f3 L = computeRadiance(ps[pidx[i]], dir, deg);
+        out[3 * i] = L.x; out[3 * i + 1] = L.y; out[3 * i + 2] = L.z;
+    }
+}
+void orc_quantize_batch(uint64_t n, const float* x, uint8_t* out) {
+    for (uint64_t i = 0; i < n; ++i) out[i] = orc_quantize(x[i]);
+}
+void orc_get_rays(const OrcParams* prm, uint64_t n, const uint32_t* xs, const uint32_t* ys, float* o, float* d, uint8_t* valid) {
+    for (uint64_t i = 0; i < n; ++i) {
+        o[3 * i] = o[3 * i + 1] = o[3 * i + 2] = d[3 * i] = d[3 * i + 1] = d[3 * i + 2] = NAN;
+        valid[i] = (uint8_t)orc_get_ray(prm, xs[i], ys[i], o + 3 * i, d + 3 * i);
+    }
+}
+void orc_refract_batch(uint64_t n, const float* d, const float* nrm, float eta, float* out_dir, float* t_hit_io, uint32_t* bounces_io) {
+    for (uint64_t i = 0; i < n; ++i) orc_refract(d + 3 * i, nrm + 3 * i, eta, out_dir + 3 * i, t_hit_io + i, bounces_io + i);
+}
+void orc_mirror_batch(uint64_t n, const float* d, const float* nrm, float* out_dir, uint32_t* bounces_io) {  // renderMirror, tracer.cuh:396-404
+    for (uint64_t i = 0; i < n; ++i) {
+        const f3 r = reflect(ld3(d + 3 * i), ld3(nrm + 3 * i));
+        out_dir[3 * i] = r.x; out_dir[3 * i + 1] = r.y; out_dir[3 * i + 2] = r.z;
+        bounces_io[i] += 1;
+    }
+}
+// Derived proxy data of each particle: A (9 floats, row-major), s, the 12 world-space vertices, the padded box; live = 0 if culled.
+void orc_proxy_data(const OrcParticle* ps, uint64_t n, float alpha_min_build, float* A9, float* s_out, float* wv36, float* box6, uint8_t* live) {
+    for (uint64_t i = 0; i < n; ++i) {
+        Proxy P;
+        live[i] = make_proxy(ps[i], (uint32_t)i, alpha_min_build, P) ? 1 : 0;
+        if (!live[i]) continue;
+        memcpy(A9 + 9 * i, P.A, sizeof(float) * 9);
+        s_out[i] = P.s;
+        memcpy(wv36 + 36 * i, P.wv, sizeof(float) * 36);
+        memcpy(box6 + 6 * i, P.lo, sizeof(float) * 3);
+        memcpy(box6 + 6 * i + 3, P.hi, sizeof(float) * 3);
+    }
+}
+// Slab test (PROXY-T) of particle pidx[i] against ray i: hit[i] = 1 and t2[2i], t2[2i+1] = (te, tx) when crossed.
+void orc_proxy_hit_batch(const OrcParticle* ps, uint64_t n, const uint32_t* pidx, float alpha_min_build, const float* o, const float* d,
+                         float* t2, uint8_t* hit) {
+    for (uint64_t i = 0; i < n; ++i) {
+        Proxy P;
+        hit[i] = 0;
+        if (!make_proxy(ps[pidx[i]], pidx[i], alpha_min_build, P)) continue;
+        hit[i] = proxy_hit_slabs(P, ld3(o + 3 * i), ld3(d + 3 * i), t2[2 * i], t2[2 * i + 1]) ? 1 : 0;
+    }
+}
+// Moller-Trumbore over an explicit triangle soup (12 vertices, 20 faces per proxy: e.g. the REFERENCE's icosahedron pushed through
+// the REFERENCE's instance matrix): nearest and farthest crossing of ray i with soup i.
+void orc_soup_hits(uint64_t n, const float* verts36, const uint32_t* idx60, const float* o, const float* d, float* t2, uint8_t* hit) {
+    for (uint64_t i = 0; i < n; ++i) {
+        const float* v = verts36 + 36 * i;
+        int cnt = 0;
+        float ts[20];
+        for (int f = 0; f < 20; ++f) {
+            float t, u, w;
+            if (tri_hit(ld3(o + 3 * i), ld3(d + 3 * i), ld3(v + 3 * idx60[3 * f]), ld3(v + 3 * idx60[3 * f + 1]), ld3(v + 3 * idx60[3 * f + 2]), t, u, w)) ts[cnt++] = t;
+        }
+        hit[i] = cnt >= 2;
+        if (cnt >= 2) { std::sort(ts, ts + cnt); t2[2 * i] = ts[0]; t2[2 * i + 1] = ts[cnt - 1]; }
+    }
+}
+
 }  // extern "C"

@@ -111,6 +111,18 @@ void orc_refract(const float d[3], const float n[3], float eta, float out_dir[3]
 void orc_transform_mesh(const float* verts, const float* normals, uint32_t n, const float transform_colmajor[16],
                         float* verts_world, float* normals_out);
 
+/* batch forms of the hooks above (tests/test_ref_pins.py: oracle vs reference-compiled code on 1e5 random inputs) */
+void orc_compute_response_batch(const OrcParticle* ps, uint64_t n, const uint32_t* pidx, const float* o, const float* d, float* out);
+void orc_sh_radiance_batch(const OrcParticle* ps, uint64_t n, const uint32_t* pidx, const float* d, uint32_t deg, int normalise, float* out);
+void orc_quantize_batch(uint64_t n, const float* x, uint8_t* out);
+void orc_get_rays(const OrcParams* prm, uint64_t n, const uint32_t* xs, const uint32_t* ys, float* o, float* d, uint8_t* valid);
+void orc_refract_batch(uint64_t n, const float* d, const float* nrm, float eta, float* out_dir, float* t_hit_io, uint32_t* bounces_io);
+void orc_mirror_batch(uint64_t n, const float* d, const float* nrm, float* out_dir, uint32_t* bounces_io);
+void orc_proxy_data(const OrcParticle* ps, uint64_t n, float alpha_min_build, float* A9, float* s_out, float* wv36, float* box6, uint8_t* live);
+void orc_proxy_hit_batch(const OrcParticle* ps, uint64_t n, const uint32_t* pidx, float alpha_min_build, const float* o, const float* d,
+                         float* t2, uint8_t* hit);
+void orc_soup_hits(uint64_t n, const float* verts36, const uint32_t* idx60, const float* o, const float* d, float* t2, uint8_t* hit);
+
 #ifdef __cplusplus
 }
 #endif

@@ -244,3 +244,262 @@ def ref_camera_uvw(eye, lookat, up, fovy, aspect):
     U, V, W = np.zeros(3, np.float32), np.zeros(3, np.float32), np.zeros(3, np.float32)
     L.ref_camera_uvw(_p(e), _p(l), _p(u), fovy, aspect, _p(U), _p(V), _p(W))
     return U, V, W
+
+
+# ---- batch forms of the KAT hooks (oracle side) -------------------------------------------------------------------
+def _f32c(a):
+    return np.ascontiguousarray(a, np.float32)
+
+
+def _u32c(a):
+    return np.ascontiguousarray(a, np.uint32)
+
+
+def compute_response_batch(particles, pidx, o, d):
+    ps, pidx, o, d = _f32c(particles), _u32c(pidx), _f32c(o), _f32c(d)
+    out = np.zeros(len(pidx), np.float32)
+    f = lib().orc_compute_response_batch
+    f.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    f.restype = None
+    f(_p(ps), len(pidx), _p(pidx), _p(o), _p(d), _p(out))
+    return out
+
+
+def sh_radiance_batch(particles, pidx, d, deg, normalise=True):
+    ps, pidx, d = _f32c(particles), _u32c(pidx), _f32c(d)
+    out = np.zeros((len(pidx), 3), np.float32)
+    f = lib().orc_sh_radiance_batch
+    f.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]
+    f.restype = None
+    f(_p(ps), len(pidx), _p(pidx), _p(d), deg, int(normalise), _p(out))
+    return out
+
+
+def quantize_batch(x):
+    x = _f32c(x)
+    out = np.zeros(x.shape, np.uint8)
+    f = lib().orc_quantize_batch
+    f.argtypes = [C.c_uint64, C.c_void_p, C.c_void_p]
+    f.restype = None
+    f(x.size, _p(x), _p(out))
+    return out
+
+
+def get_rays(params: OrcParams, xs, ys):
+    xs, ys = _u32c(xs), _u32c(ys)
+    o, d = np.zeros((len(xs), 3), np.float32), np.zeros((len(xs), 3), np.float32)
+    valid = np.zeros(len(xs), np.uint8)
+    f = lib().orc_get_rays
+    f.argtypes = [C.POINTER(OrcParams), C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    f.restype = None
+    f(C.byref(params), len(xs), _p(xs), _p(ys), _p(o), _p(d), _p(valid))
+    return o, d, valid.astype(bool)
+
+
+def refract_batch(d, n, eta, t_hit, bounces):
+    d, n = _f32c(d), _f32c(n)
+    out = np.zeros_like(d)
+    t, b = _f32c(t_hit).copy(), _u32c(bounces).copy()
+    f = lib().orc_refract_batch
+    f.argtypes = [C.c_uint64, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+    f.restype = None
+    f(len(d), _p(d), _p(n), eta, _p(out), _p(t), _p(b))
+    return out, t, b
+
+
+def mirror_batch(d, n, bounces):
+    d, n = _f32c(d), _f32c(n)
+    out = np.zeros_like(d)
+    b = _u32c(bounces).copy()
+    f = lib().orc_mirror_batch
+    f.argtypes = [C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    f.restype = None
+    f(len(d), _p(d), _p(n), _p(out), _p(b))
+    return out, b
+
+
+def proxy_data(particles, alpha_min=0.01):
+    ps = _f32c(particles)
+    n = ps.shape[0]
+    A, s = np.zeros((n, 3, 3), np.float32), np.zeros(n, np.float32)
+    wv, box, live = np.zeros((n, 12, 3), np.float32), np.zeros((n, 6), np.float32), np.zeros(n, np.uint8)
+    f = lib().orc_proxy_data
+    f.argtypes = [C.c_void_p, C.c_uint64, C.c_float] + [C.c_void_p] * 5
+    f.restype = None
+    f(_p(ps), n, alpha_min, _p(A), _p(s), _p(wv), _p(box), _p(live))
+    return dict(A=A, s=s, wv=wv, box=box, live=live.astype(bool))
+
+
+def proxy_hit_batch(particles, pidx, o, d, alpha_min=0.01):
+    ps, pidx, o, d = _f32c(particles), _u32c(pidx), _f32c(o), _f32c(d)
+    t2, hit = np.zeros((len(pidx), 2), np.float32), np.zeros(len(pidx), np.uint8)
+    f = lib().orc_proxy_hit_batch
+    f.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    f.restype = None
+    f(_p(ps), len(pidx), _p(pidx), alpha_min, _p(o), _p(d), _p(t2), _p(hit))
+    return t2, hit.astype(bool)
+
+
+def soup_hits(verts, idx60, o, d):
+    verts, idx60, o, d = _f32c(verts), _u32c(idx60), _f32c(o), _f32c(d)
+    n = verts.shape[0]
+    t2, hit = np.zeros((n, 2), np.float32), np.zeros(n, np.uint8)
+    f = lib().orc_soup_hits
+    f.argtypes = [C.c_uint64] + [C.c_void_p] * 6
+    f.restype = None
+    f(n, _p(verts), _p(idx60), _p(o), _p(d), _p(t2), _p(hit))
+    return t2, hit.astype(bool)
+
+
+# ---- the reference's own hot-path math (oracle/_ref, ref_math_shim.cpp) ---------------------------------------------
+_ref = None
+
+
+def ref():
+    """ctypes handle of oracle/_ref/libref_host.so with the math entry points typed (raises if the library is absent or older
+    than ref_math_shim.cpp: rebuild with `make -C oracle ref` in a container that has /root/reference)."""
+    global _ref
+    if _ref is None:
+        L = C.CDLL(REF_PATH)
+        if not hasattr(L, "ref_layout"):
+            raise RuntimeError(f"{REF_PATH} predates ref_math_shim.cpp: run `make -C {_HERE} ref`")
+        V = C.c_void_p
+        L.ref_layout.argtypes = [V]
+        L.ref_constants.argtypes = [V]
+        L.ref_param_defaults.argtypes = [C.c_float, V, V]
+        L.ref_quantize.argtypes = [C.c_uint64, V, V]
+        L.ref_get_rays.argtypes = [C.c_int, C.c_uint64, V, V, V, V, V, V, C.c_int, C.c_int, V, V, V]
+        L.ref_compute_response.argtypes = [V, C.c_uint64, V, V, V, V]
+        L.ref_sh_radiance.argtypes = [V, C.c_uint64, V, V, C.c_uint32, C.c_int, V]
+        L.ref_refract.argtypes = [C.c_uint64, V, V, C.c_float, V, V, V]
+        L.ref_mirror.argtypes = [C.c_uint64, V, V, V, V]
+        L.ref_proxy_transforms.argtypes = [V, C.c_uint64, C.c_float, V]
+        L.ref_icosahedron.argtypes = [V, V]
+        L.ref_primitive.argtypes = [C.c_int, V, V, V, V, V, V]
+        L.ref_normal_transform.argtypes = [C.c_uint64, V, V, V]
+        L.ref_pack_transform.argtypes = [V, V]
+        L.ref_placement.argtypes = [V, V, V]
+        L.ref_trs.argtypes = [V, C.c_float, C.c_float, V]
+        for n in ("ref_layout ref_constants ref_param_defaults ref_quantize ref_get_rays ref_compute_response ref_sh_radiance ref_refract "
+                  "ref_mirror ref_proxy_transforms ref_icosahedron ref_primitive ref_normal_transform ref_pack_transform ref_placement ref_trs").split():
+            getattr(L, n).restype = None
+        _ref = L
+    return _ref
+
+
+REF_LAYOUT_NAMES = ["sizeof_Params", "output_buffer", "width", "height", "sh_degree_max", "eye", "U", "V", "W", "t_min", "t_max",
+                    "minTransmittance", "alpha_min", "handle", "d_particles", "mesh_handle", "mode_fisheye", "d_meshes", "type", "traceState",
+                    "sizeof_GaussianParticle", "gp_position", "gp_scale", "gp_rotation", "gp_opacity", "gp_sh",
+                    "sizeof_Mesh", "mesh_faces", "mesh_vertex_normals", "mesh_type_enum", "MaxNumHitPerTrace", "timeout_bounces"]
+
+
+def ref_layout():
+    out = np.zeros(32, np.uint64)
+    ref().ref_layout(_p(out))
+    return dict(zip(REF_LAYOUT_NAMES, (int(v) for v in out)))
+
+
+def ref_constants():
+    out = np.zeros(24, np.float32)
+    ref().ref_constants(_p(out))
+    return out
+
+
+def ref_param_defaults(alpha_min=0.01):
+    f, i = np.zeros(4, np.float32), np.zeros(3, np.int32)
+    ref().ref_param_defaults(alpha_min, _p(f), _p(i))
+    return f, i
+
+
+def ref_quantize(x):
+    x = _f32c(x)
+    out = np.zeros(x.shape, np.uint8)
+    ref().ref_quantize(x.size, _p(x), _p(out))
+    return out
+
+
+def ref_get_rays(fisheye, xs, ys, U, V, W, eye, width, height):
+    xs, ys = _u32c(xs), _u32c(ys)
+    U, V, W, eye = _f32c(U), _f32c(V), _f32c(W), _f32c(eye)
+    o, d = np.zeros((len(xs), 3), np.float32), np.zeros((len(xs), 3), np.float32)
+    valid = np.zeros(len(xs), np.uint8)
+    ref().ref_get_rays(int(fisheye), len(xs), _p(xs), _p(ys), _p(U), _p(V), _p(W), _p(eye), width, height, _p(o), _p(d), _p(valid))
+    return o, d, valid.astype(bool)
+
+
+def ref_compute_response(particles, pidx, o, d):
+    ps, pidx, o, d = _f32c(particles), _u32c(pidx), _f32c(o), _f32c(d)
+    out = np.zeros(len(pidx), np.float32)
+    ref().ref_compute_response(_p(ps), len(pidx), _p(pidx), _p(o), _p(d), _p(out))
+    return out
+
+
+def ref_sh_radiance(particles, pidx, d, deg, normalise=True):
+    ps, pidx, d = _f32c(particles), _u32c(pidx), _f32c(d)
+    out = np.zeros((len(pidx), 3), np.float32)
+    ref().ref_sh_radiance(_p(ps), len(pidx), _p(pidx), _p(d), deg, int(normalise), _p(out))
+    return out
+
+
+def ref_refract(d, n, eta, t_hit, bounces):
+    d, n = _f32c(d), _f32c(n)
+    out = np.zeros_like(d)
+    t, b = _f32c(t_hit).copy(), _u32c(bounces).copy()
+    ref().ref_refract(len(d), _p(d), _p(n), eta, _p(out), _p(t), _p(b))
+    return out, t, b
+
+
+def ref_mirror(d, n, bounces):
+    d, n = _f32c(d), _f32c(n)
+    out = np.zeros_like(d)
+    b = _u32c(bounces).copy()
+    ref().ref_mirror(len(d), _p(d), _p(n), _p(out), _p(b))
+    return out, b
+
+
+def ref_proxy_transforms(particles, alpha_min=0.01):
+    ps = _f32c(particles)
+    out = np.zeros((ps.shape[0], 3, 4), np.float32)
+    ref().ref_proxy_transforms(_p(ps), ps.shape[0], alpha_min, _p(out))
+    return out
+
+
+def ref_icosahedron():
+    v, i = np.zeros((12, 3), np.float32), np.zeros(60, np.uint32)
+    ref().ref_icosahedron(_p(v), _p(i))
+    return v, i
+
+
+def ref_primitive(kind, position):
+    pos = _f32c(position)
+    counts, T = np.zeros(2, np.uint64), np.zeros(16, np.float32)
+    ref().ref_primitive(kind, _p(pos), None, None, None, _p(counts), _p(T))
+    v, n = np.zeros((int(counts[0]), 3), np.float32), np.zeros((int(counts[0]), 3), np.float32)
+    idx = np.zeros(int(counts[1]), np.uint32)
+    ref().ref_primitive(kind, _p(pos), _p(v), _p(n), _p(idx), _p(counts), _p(T))
+    return dict(vertices=v, normals=n, indices=idx, transform=T.reshape(4, 4))
+
+
+def ref_normal_transform(normals, transform_colmajor16):
+    nn, T = _f32c(normals), _f32c(transform_colmajor16).reshape(16)
+    out = np.zeros_like(nn)
+    ref().ref_normal_transform(nn.shape[0], _p(nn), _p(T), _p(out))
+    return out
+
+
+def ref_pack_transform(transform_colmajor16):
+    T, out = _f32c(transform_colmajor16).reshape(16), np.zeros((3, 4), np.float32)
+    ref().ref_pack_transform(_p(T), _p(out))
+    return out
+
+
+def ref_placement(eye, lookat):
+    e, l, out = _f32c(eye), _f32c(lookat), np.zeros(3, np.float32)
+    ref().ref_placement(_p(e), _p(l), _p(out))
+    return out
+
+
+def ref_trs(t, rot_y_deg, s):
+    t, out = _f32c(t), np.zeros(16, np.float32)
+    ref().ref_trs(_p(t), rot_y_deg, s, _p(out))
+    return out.reshape(4, 4)
