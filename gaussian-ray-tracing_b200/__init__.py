@@ -88,7 +88,7 @@ class GrtCounters(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in (
         "rays", "segments", "rounds", "hits_gathered", "hits_shaded", "warp_nodes", "warp_leaf_prims",
         "warp_rounds", "stack_overflow", "kernel_launches", "warp_prims_hit", "warp_consume_iters", "lanes_repass",
-        "order_violations", "warp_dfs_fallbacks", "warp_candidate_iters")] + [("dbg", C.c_uint64 * 8)]
+        "order_violations", "warp_dfs_fallbacks", "warp_candidate_iters")] + [("dbg", C.c_uint64 * 8), ("warp_per_ray_passes", C.c_uint64)]
 
 
 # every symbol include/grt.h declares (tests check that the .so exports all of them)
@@ -145,6 +145,8 @@ def load_libgrt():
         "grtSetParticlesRaw": [vp, vp, u64, u32, C.POINTER(u32), f32],
         "grtLoadPly": [vp, C.c_char_p, f32, C.POINTER(u64), C.POINTER(f32)],
         "grtGetParticles": [vp, vp, u64],
+        "grtLaunchRows": [vp, vp, C.POINTER(GrtParams), u32, u32, u32],
+        "grtGetAbiLayout": [C.POINTER(u64)],
     }
     for name, args in sig.items():
         fn = getattr(lib, name)
@@ -281,6 +283,10 @@ class Context:
 
     def launch_tile(self, params: GrtParams, x0, y0, w, h, stream=None):
         self._ck(self.lib.grtLaunchTile(self.h, stream, C.byref(params), x0, y0, w, h))
+
+    def launch_rows(self, params: GrtParams, band_rows: int, band_stride: int, band_offset: int, stream=None):
+        """One launch for the row bands b with b % band_stride == band_offset (bands of band_rows rows): rank r of G GPUs."""
+        self._ck(self.lib.grtLaunchRows(self.h, stream, C.byref(params), band_rows, band_stride, band_offset))
 
     def launch_batch(self, params_list, stream=None):
         arr = (GrtParams * len(params_list))(*params_list)

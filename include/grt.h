@@ -89,6 +89,7 @@ typedef struct grtCounters {
     uint64_t warp_dfs_fallbacks; /* packets whose best-first queue filled up and that redid the pass depth-first */
     uint64_t warp_candidate_iters; /* warp iterations of the per-ray exact proxy test loop */
     uint64_t dbg[8];          /* free-form profiling counters of the counting kernel variant (meaning: DESIGN.md) */
+    uint64_t warp_per_ray_passes; /* traversal passes that ran ray by ray (divergent secondary packets, trace_rays_dfs) */
 } grtCounters;
 
 typedef struct grtContext grtContext;

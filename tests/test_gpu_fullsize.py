@@ -8,6 +8,7 @@ import numpy as np
 import pytest
 
 from conftest import make_scene, psnr
+from gpu_util import parity_stats
 
 pytestmark = pytest.mark.gpu
 
@@ -57,19 +58,14 @@ def _launch(ctx, P, *, tile=None, counters=False, want_float=False):
     return img, f32, c
 
 
-def _band_parity(orc, rec, P, img, f32, *, meshes=None, label=""):
-    S = orc.Scene(rec, 0.01)
-    if meshes:
-        S.set_meshes(meshes)
-    ora = S.render(orc.params_from_grt(P), K=7, rect=BAND)
-    y0, y1 = BAND[1], BAND[1] + BAND[3]
-    flags = ora["flags"][y0:y1].astype(bool)
-    diff = np.abs(f32[y0:y1] - ora["rgb32f"][y0:y1]).max(axis=2)
-    lsb = np.abs(img[y0:y1].astype(int) - ora["rgb8"][y0:y1].astype(int)).max(axis=2)
-    res = dict(max_abs=float(diff[~flags].max()), flag_frac=float(flags.mean()), lsb=int(lsb[~flags].max()),
-               psnr=psnr(np.clip(f32[y0:y1], 0, 1), np.clip(ora["rgb32f"][y0:y1], 0, 1)))
-    print(f"[full-size parity {label}] {res}")
-    assert res["flag_frac"] <= 0.03 and res["max_abs"] <= 1e-3 and res["lsb"] <= 1 and res["psnr"] >= 50.0, res  # north_star tolerances
+def _band_parity(orc, rec, P, img, f32, *, meshes=None, label="", band=None, scene=None, max_tie_frac=0.01):
+    band = band or BAND
+    S = scene or orc.Scene(rec, 0.01)
+    S.set_meshes(meshes or [])
+    ora = S.render(orc.params_from_grt(P), K=7, rect=band)
+    y0, y1 = band[1], band[1] + band[3]
+    parity_stats(f32[y0:y1], img[y0:y1], ora["rgb32f"][y0:y1], ora["rgb8"][y0:y1], ora["flags"][y0:y1], label=f"full-size {label}",
+                 max_tie_frac=max_tie_frac)
     return ora
 
 
@@ -142,13 +138,23 @@ def test_config4_mirrors_1m_1080p(ctx, grt, orc, scene1m):
     _band_parity(orc, rec, P, img, f32, meshes=meshes, label="config 4 mirrors")
     part, _, _ = _launch(ctx, P, tile=(640, 400, 700, 300))
     assert np.array_equal(part[400:700, 640:1340], img[400:700, 640:1340])
+    # NORMAL and GLASS shading of the same primitives at full size (MeshType 1, 2; tracer.cuh:406-482)
+    S = orc.Scene(rec, 0.01)
+    for mesh_type, name in [(1, "normal"), (2, "glass")]:
+        P.type = mesh_type
+        img_t, f32_t, c = _launch(ctx, P, counters=True, want_float=True)
+        assert c["stack_overflow"] == 0 and c["order_violations"] == 0
+        assert not np.array_equal(img_t, img)
+        _band_parity(orc, rec, P, img_t, f32_t, meshes=meshes, label=f"config 4 primitives, {name}", scene=S)
+    P.type = 0
     ctx.set_meshes([])
     ctx.build_mesh_accel()
     P.mesh_handle, P.d_meshes = 0, None
 
 
-def test_config5_6m_4k_camera_batch(ctx, grt):
-    """6M Gaussians, 3840x2160, cameras of the 64-camera ring; grtLaunchBatch == single launches."""
+def test_config5_6m_4k_camera_batch(ctx, grt, orc):
+    """6M Gaussians, 3840x2160, cameras of the 64-camera ring: an oracle band of each camera's frame; grtLaunchBatch == single
+    launches; the row-band partition of one camera over 4 'ranks' (grtLaunchRows) reproduces the frame bit for bit."""
     n, w, h = 6_000_000, 3840, 2160
     rec = grt.activate(grt.synth_ply_properties(n, 1003))
     ctx.set_particles(rec, 0.01)
@@ -157,15 +163,20 @@ def test_config5_6m_4k_camera_batch(ctx, grt):
     assert info["n_live"] > 0.99 * n
     cam = grt.default_camera(rec)
     frames, params = [], []
+    S5 = None
     for k in (0, 17):
         th = 2 * np.pi * k / 64
         eye = np.array([3 * np.sin(th), 0.5, 3 * np.cos(th)], np.float32)
         U, V, Wv = grt.camera_uvw(eye, cam["lookat"], cam["up"], 60.0, float(np.float32(w) / np.float32(h)))
         P = grt.make_params(w, h, eye, U, V, Wv, sh_degree_max=3)
         P.handle, P.d_particles = handle, dpart
-        img, _, c = _launch(ctx, P, counters=True)
+        img, f32, c = _launch(ctx, P, counters=True, want_float=True)
         assert c["rays"] == w * h and c["stack_overflow"] == 0 and c["order_violations"] == 0
         assert img.max() > 0
+        if S5 is None:
+            S5 = orc.Scene(rec, 0.01)
+        _band_parity(orc, rec, P, img, f32, label=f"config 5 camera {k}", band=(0, 1076, w, 8), scene=S5)
+        del f32
         frames.append(img)
         params.append(P)
     bufs = [ctx.malloc(w * h * 3) for _ in params]
@@ -176,4 +187,14 @@ def test_config5_6m_4k_camera_batch(ctx, grt):
     for b, ref in zip(bufs, frames):
         assert np.array_equal(ctx.to_host(b, (h, w, 3), np.uint8), ref)
         ctx.free(b)
+    # one 4K frame as 4 interleaved row-band launches (what 4 ranks would trace): the union is the frame
+    d = ctx.malloc(w * h * 3)
+    ctx.memset(d, 0, w * h * 3)
+    params[0].output_buffer = d
+    for r in range(4):
+        ctx.launch_rows(params[0], 8, 4, r)
+    ctx.sync()
+    assert np.array_equal(ctx.to_host(d, (h, w, 3), np.uint8), frames[0])
+    ctx.free(d)
+    del S5
     ctx.set_particles(rec[:0], 0.01)

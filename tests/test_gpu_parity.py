@@ -6,7 +6,7 @@ import numpy as np
 import pytest
 
 from conftest import make_scene
-from gpu_util import compare, gpu_render
+from gpu_util import check_traces, compare, gpu_render
 
 pytestmark = pytest.mark.gpu
 
@@ -19,21 +19,11 @@ def _oracle(orc, rec, P, meshes=None, **kw):
 
 
 def _check_traces(gpu, ora, rect, W, flags, trace_max):
-    x0, y0, w, h = rect
-    n_cmp = n_bad = 0
-    for j in range(h):
-        for i in range(w):
-            slot = j * w + i
-            if flags[y0 + j, x0 + i]:
-                continue
-            n_cmp += 1
-            c = int(ora["trace_counts"][slot])
-            assert int(gpu.trace_counts[slot]) == c, (i, j, int(gpu.trace_counts[slot]), c)
-            k = min(c, trace_max)
-            if not np.array_equal(gpu.trace_ids[slot, :k], ora["trace_ids"][slot, :k]):
-                n_bad += 1
-    print(f"[traces] compared {n_cmp} pixels, {n_bad} sequence mismatches")
-    assert n_cmp > 0 and n_bad == 0
+    return check_traces(gpu, ora, rect, flags, trace_max)
+
+
+def _trace_pixels(rect, width):
+    return np.array([(rect[1] + j) * width + rect[0] + i for j in range(rect[3]) for i in range(rect[2])], np.uint32)
 
 
 @pytest.mark.parametrize("deg", [0, 1, 2, 3])
@@ -64,9 +54,14 @@ def test_config1_100k_800x800(ctx, grt, orc):
 
 def test_fisheye_parity(ctx, grt, orc):
     rec, P, _ = make_scene(grt, 20_000, 103, 160, 160, deg=3, fisheye=True)
-    ora = _oracle(orc, rec, P)
-    gpu = gpu_render(ctx, grt, rec, P)
-    compare(gpu, ora, label="fisheye", max_flag_frac=0.02)
+    # hit-ID sequences on a block at the centre (directions change sign inside packets: the incoherent node test) and one
+    # at the rim of the fisheye circle (strongly divergent rays, pixels with r > 1 next to traced ones)
+    for rect in [(64, 68, 32, 24), (0, 60, 40, 24)]:
+        ora = _oracle(orc, rec, P, trace_pixels=_trace_pixels(rect, P.width), trace_max=96)
+        gpu = gpu_render(ctx, grt, rec, P, trace_rect=rect, trace_max=96, counters=True)
+        compare(gpu, ora, label=f"fisheye {rect}", max_flag_frac=0.02)
+        check_traces(gpu, ora, rect, ora["flags"], 96, min_compared=200)
+        assert gpu.counters["stack_overflow"] == 0 and gpu.counters["order_violations"] == 0
     # r > 1 corners are DEFINED black
     assert gpu.rgb8[0, 0].tolist() == [0, 0, 0] and gpu.rgb8[-1, -1].tolist() == [0, 0, 0]
 
@@ -82,10 +77,19 @@ def _config4_meshes(grt):
 def test_mesh_modes_parity(ctx, grt, orc, mesh_type):
     rec, P, _ = make_scene(grt, 20_000, 104, 192, 128, deg=3, mesh_type=mesh_type)
     meshes = _config4_meshes(grt)
-    ora = _oracle(orc, rec, P, meshes=meshes)
-    gpu = gpu_render(ctx, grt, rec, P, meshes=meshes)
+    # hit-ID sequences (all segments of a pixel, in order) on a full-width band through the plane and the sphere: mirror-sphere
+    # rim packets fan out and take the per-ray walk (trace_rays_dfs), which must yield the same sequences as the packet mode
+    rect, tmax = (0, 40, 192, 48), 160
+    ora = _oracle(orc, rec, P, meshes=meshes, trace_pixels=_trace_pixels(rect, P.width), trace_max=tmax)
+    gpu = gpu_render(ctx, grt, rec, P, meshes=meshes, trace_rect=rect, trace_max=tmax, counters=True)
     # secondary rays are bit-reproduced too (un-fused ray-path arithmetic), so the same bar applies
     compare(gpu, ora, label=f"mesh type {mesh_type}", max_flag_frac=0.03)
+    check_traces(gpu, ora, rect, ora["flags"], tmax, min_compared=5000)
+    c = gpu.counters
+    assert c["stack_overflow"] == 0 and c["order_violations"] == 0
+    print("mesh type", mesh_type, "segments/ray", c["segments"] / c["rays"], "per-ray passes", c["warp_per_ray_passes"])
+    if mesh_type != 1:
+        assert c["segments"] > c["rays"] and c["warp_per_ray_passes"] > 0  # the divergent (per-ray) mode was exercised
     no_mesh = _oracle(orc, rec, P)
     assert np.abs(no_mesh["rgb32f"] - ora["rgb32f"]).max() > 0.01  # the primitives are actually in view
 
@@ -96,6 +100,41 @@ def test_tile_and_batch_equal_full_frame(ctx, grt, orc):
     part = gpu_render(ctx, grt, rec, P, tile=(16, 16, 50, 33))
     assert np.array_equal(part.rgb8[16:49, 16:66], full.rgb8[16:49, 16:66])
     assert part.rgb8[:16].max() == 0 and part.rgb8[49:].max() == 0  # untouched outside the tile
+
+
+@pytest.mark.parametrize("size", [(100, 70), (160, 121)])
+def test_row_bands_union_is_frame(ctx, grt, size):
+    """grtLaunchRows: G launches with band_stride = G, band_offset = r write disjoint row bands whose union is grtLaunch's frame,
+    bit for bit (bands are multiples of the 8-row packet grid, so every packet is the same packet)."""
+    W, H = size
+    rec, P, _ = make_scene(grt, 5_000, 105, W, H, deg=2)
+    full = gpu_render(ctx, grt, rec, P)
+    ctx.set_particles(rec, 0.01)
+    P.handle, P.d_particles = ctx.build_particle_accel()
+    d = ctx.malloc(W * H * 3)
+    P.output_buffer = d
+    for band_rows, G in [(8, 2), (8, 3), (16, 4), (8, 8), (24, 5)]:
+        ctx.memset(d, 0, W * H * 3)
+        seen = np.zeros((H, W), bool)
+        for r in range(G):
+            before = ctx.to_host(d, (H, W, 3), np.uint8)
+            ctx.launch_rows(P, band_rows, G, r)
+            ctx.sync()
+            after = ctx.to_host(d, (H, W, 3), np.uint8)
+            own = np.zeros(H, bool)
+            for b in range(r, (H + band_rows - 1) // band_rows, G):
+                own[b * band_rows:(b + 1) * band_rows] = True
+            assert np.array_equal(after[~own], before[~own])        # nothing outside the owned bands is written
+            assert not seen[own].any()
+            seen[own] = True
+        assert seen.all()
+        assert np.array_equal(ctx.to_host(d, (H, W, 3), np.uint8), full.rgb8), (band_rows, G)
+    with pytest.raises(grt.GrtError):
+        ctx.launch_rows(P, 12, 2, 0)      # not a multiple of the packet grid
+    with pytest.raises(grt.GrtError):
+        ctx.launch_rows(P, 8, 2, 2)       # offset outside the stride
+    ctx.free(d)
+    P.output_buffer = None
 
 
 def test_render_host_e2e(ctx, grt, orc):

@@ -68,6 +68,31 @@ def test_rebuild_time_1m(grt, ctx):
         wall.append((time.perf_counter() - t) * 1e3)
         ms.append(ctx.build_info()["build_ms"])
     ctx.validate_accel(0)
-    print("1M rebuild device ms", [round(m, 2) for m in ms], "wall ms", [round(w, 2) for w in wall])
-    assert min(ms[1:]) < ms[0] * 1.05 and min(wall[1:]) < 10.0
+    print("1M rebuild device ms", [round(m, 2) for m in ms], "wall ms", [round(w, 2) for w in wall],
+          "Gprims/s", round(1e-6 / (min(ms[1:]) * 1e-3), 3))
+    # >= 1 Gprims/s would be 1.0 ms; measured 0.98 ms on a quiet B200 -- the bound leaves room for clock and
+    # allocator jitter of a shared box, not for a regression to the 2 ms of the unpooled builder
+    assert min(ms[1:]) < 1.5, ms
+    assert min(wall[1:]) < 3.0, wall
     ctx.set_particles(rec[:0], 0.01)
+
+
+def test_rebuilt_accel_renders_like_the_oracle(grt, ctx, orc):
+    """A frame after grtSetParticles + rebuild is compared with the ORACLE of the new particle set (not only with a fresh
+    context): moved particles, a changed count and changed opacities (some cross the cull threshold alpha_min)."""
+    from gpu_util import compare
+    W, H = 160, 96
+    rec, P, _ = make_scene(grt, 30_000, 21, W, H, deg=3)
+    gpu_render(ctx, grt, rec, P)                                   # the accel the next builds reuse
+    rng = np.random.default_rng(3)
+    rec2 = rec[: 25_000].copy()
+    rec2[:, 0:3] += rng.normal(0, 0.05, (len(rec2), 3)).astype(np.float32)
+    rec2[::7, 10] = np.float32(0.009)                              # culled now (opacity <= alpha_min)
+    rec2[1::7, 10] = np.float32(0.95)
+    for frame in (rec2, rec):                                      # shrink + move, then grow back
+        gpu = gpu_render(ctx, grt, frame, P, counters=True)
+        S = orc.Scene(frame, 0.01)
+        ora = S.render(orc.params_from_grt(P), K=7)
+        compare(gpu, ora, label=f"rebuilt accel, {len(frame)} particles")
+        assert ctx.build_info()["n_live"] == S.live_count()
+        assert gpu.counters["stack_overflow"] == 0
