@@ -175,7 +175,8 @@ def test_config5_6m_4k_camera_batch(ctx, grt, orc):
         assert img.max() > 0
         if S5 is None:
             S5 = orc.Scene(rec, 0.01)
-        _band_parity(orc, rec, P, img, f32, label=f"config 5 camera {k}", band=(0, 1076, w, 8), scene=S5)
+        # (6M particles: six times the density of config 2 along a ray, hence more equal-t ties per pixel -- 1.1 % of the band)
+        _band_parity(orc, rec, P, img, f32, label=f"config 5 camera {k}", band=(0, 1076, w, 8), scene=S5, max_tie_frac=0.02)
         del f32
         frames.append(img)
         params.append(P)
