@@ -98,7 +98,7 @@ GRT_SYMBOLS = [
     "grtEnableCounters", "grtGetCounters", "grtGetBuildInfo", "grtValidateAccel", "grtLastLaunchMs", "grtMalloc",
     "grtFree", "grtMallocHost", "grtFreeHost", "grtMemcpyDtoH", "grtMemcpyHtoD", "grtMemset", "grtStreamCreate",
     "grtStreamDestroy", "grtStreamSynchronize", "grtDebugRadixSort", "grtSetParticlesRaw", "grtLoadPly", "grtGetParticles",
-    "grtLaunchRows", "grtGetAbiLayout",
+    "grtLaunchRows", "grtGetAbiLayout", "grtCommGetUniqueId", "grtCommInit", "grtCommDestroy", "grtGatherFrames", "grtGatherBands",
 ]
 
 _lib = None
@@ -147,6 +147,11 @@ def load_libgrt():
         "grtGetParticles": [vp, vp, u64],
         "grtLaunchRows": [vp, vp, C.POINTER(GrtParams), u32, u32, u32],
         "grtGetAbiLayout": [C.POINTER(u64)],
+        "grtCommGetUniqueId": [vp],
+        "grtCommInit": [vp, i32, i32, vp],
+        "grtCommDestroy": [vp],
+        "grtGatherFrames": [vp, vp, vp, C.c_size_t, vp, i32],
+        "grtGatherBands": [vp, vp, vp, u32, u32, u32, i32],
     }
     for name, args in sig.items():
         fn = getattr(lib, name)
@@ -287,6 +292,27 @@ class Context:
     def launch_rows(self, params: GrtParams, band_rows: int, band_stride: int, band_offset: int, stream=None):
         """One launch for the row bands b with b % band_stride == band_offset (bands of band_rows rows): rank r of G GPUs."""
         self._ck(self.lib.grtLaunchRows(self.h, stream, C.byref(params), band_rows, band_stride, band_offset))
+
+    # ---- multi-GPU exchange (one context = one rank)
+    @staticmethod
+    def comm_unique_id() -> bytes:
+        buf = (C.c_uint8 * 128)()
+        if load_libgrt().grtCommGetUniqueId(buf):
+            raise GrtError(load_libgrt().grtGetLastError(None).decode())
+        return bytes(buf)
+
+    def comm_init(self, nranks: int, rank: int, unique_id: bytes):
+        buf = (C.c_uint8 * 128).from_buffer_copy(unique_id)
+        self._ck(self.lib.grtCommInit(self.h, nranks, rank, buf))
+
+    def comm_destroy(self):
+        self._ck(self.lib.grtCommDestroy(self.h))
+
+    def gather_frames(self, d_send: int, nbytes: int, d_recv_all, root: int = 0, stream=None):
+        self._ck(self.lib.grtGatherFrames(self.h, stream, d_send, nbytes, d_recv_all, root))
+
+    def gather_bands(self, d_frame: int, width: int, height: int, band_rows: int = 8, root: int = 0, stream=None):
+        self._ck(self.lib.grtGatherBands(self.h, stream, d_frame, width, height, band_rows, root))
 
     def launch_batch(self, params_list, stream=None):
         arr = (GrtParams * len(params_list))(*params_list)

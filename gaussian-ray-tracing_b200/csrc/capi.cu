@@ -8,6 +8,7 @@
 #include <string>
 #include <vector>
 
+#include <dlfcn.h>
 #include <fcntl.h>
 #include <sys/mman.h>
 #include <sys/stat.h>
@@ -75,7 +76,54 @@ struct grtContext {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool ev_valid = false;
     grtBuildInfo info{};
+    // multi-GPU exchange (framebuffer gather): an NCCL communicator of one rank per GPU, bound through dlopen
+    void* comm = nullptr;
+    int comm_rank = 0, comm_nranks = 1;
 };
+
+// ---- NCCL, bound at run time (libnccl.so.2: the copy already loaded into the process -- torch's -- or the system one), so that
+// libgrt.so loads on machines without NCCL and single-GPU users pay nothing.  Only the calls the framebuffer gather needs.
+namespace {
+struct NcclApi {
+    void* lib = nullptr;
+    int (*GetUniqueId)(void*) = nullptr;
+    void* CommInitRank = nullptr;   // int ncclCommInitRank(ncclComm_t*, int, ncclUniqueId /* 128-byte struct BY VALUE */, int): cast at the call
+    int (*CommDestroy)(void*) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    int (*Send)(const void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*Recv)(void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    int (*GetVersion)(int*) = nullptr;
+};
+struct NcclId { char b[128]; };
+NcclApi g_nccl;
+const char* nccl_bind() {
+    if (g_nccl.lib) return nullptr;
+    void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) return "libnccl.so.2 not found (multi-GPU gather needs NCCL)";
+    auto sym = [&](const char* n) { return dlsym(h, n); };
+    g_nccl.GetUniqueId = (int (*)(void*))sym("ncclGetUniqueId");
+    g_nccl.CommInitRank = sym("ncclCommInitRank");
+    g_nccl.CommDestroy = (int (*)(void*))sym("ncclCommDestroy");
+    g_nccl.GroupStart = (int (*)())sym("ncclGroupStart");
+    g_nccl.GroupEnd = (int (*)())sym("ncclGroupEnd");
+    g_nccl.Send = (int (*)(const void*, size_t, int, int, void*, cudaStream_t))sym("ncclSend");
+    g_nccl.Recv = (int (*)(void*, size_t, int, int, void*, cudaStream_t))sym("ncclRecv");
+    g_nccl.GetErrorString = (const char* (*)(int))sym("ncclGetErrorString");
+    g_nccl.GetVersion = (int (*)(int*))sym("ncclGetVersion");
+    if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.CommDestroy || !g_nccl.GroupStart || !g_nccl.GroupEnd || !g_nccl.Send || !g_nccl.Recv)
+        return "libnccl.so.2 lacks a required symbol";
+    g_nccl.lib = h;
+    return nullptr;
+}
+}  // namespace
+#define NC(ctx, call)                                                                                                          \
+    do {                                                                                                                       \
+        int r_ = (call);                                                                                                       \
+        if (r_) return fail(ctx, "%s failed: %s (%s:%d)", #call, g_nccl.GetErrorString ? g_nccl.GetErrorString(r_) : "nccl error", __FILE__, __LINE__); \
+    } while (0)
 
 static std::string g_create_error;
 
@@ -168,6 +216,7 @@ int grtDestroy(grtContext* c) {
     c->scratch.release();
     c->mesh_pool.release();
     cudaFree(c->m_nodes);
+    if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     if (c->ev_b0) cudaEventDestroy(c->ev_b0);
     if (c->ev_b1) cudaEventDestroy(c->ev_b1);
@@ -710,6 +759,80 @@ int grtSetDebugOutputs(grtContext* c, float* d_rgb32f, uint32_t* d_trace_ids, ui
     c->tx0 = tx0; c->ty0 = ty0; c->tw = tw; c->th = th; c->trace_max = trace_max;
     return 0;
 }
+// ---------------------------------------------------------------- multi-GPU: framebuffer gather over NCCL
+int grtCommGetUniqueId(uint8_t out128[128]) {
+    if (!out128) return 1;
+    if (const char* e = nccl_bind()) return fail(nullptr, "grtCommGetUniqueId: %s", e);
+    NcclId id;
+    int r = g_nccl.GetUniqueId(&id);
+    if (r) return fail(nullptr, "ncclGetUniqueId failed: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?");
+    memcpy(out128, id.b, 128);
+    return 0;
+}
+int grtCommInit(grtContext* c, int nranks, int rank, const uint8_t id128[128]) {
+    if (!c || !id128) return 1;
+    if (nranks < 1 || rank < 0 || rank >= nranks) return fail(c, "grtCommInit: rank %d of %d", rank, nranks);
+    if (c->comm) return fail(c, "grtCommInit: this context already has a communicator");
+    if (const char* e = nccl_bind()) return fail(c, "grtCommInit: %s", e);
+    DEV(c);
+    NcclId id;
+    memcpy(id.b, id128, 128);
+    typedef int (*init_fn)(void**, int, NcclId, int);
+    NC(c, ((init_fn)g_nccl.CommInitRank)(&c->comm, nranks, id, rank));
+    c->comm_rank = rank; c->comm_nranks = nranks;
+    return 0;
+}
+int grtCommDestroy(grtContext* c) {
+    if (!c) return 1;
+    if (c->comm) { DEV(c); g_nccl.CommDestroy(c->comm); c->comm = nullptr; }
+    c->comm_rank = 0; c->comm_nranks = 1;
+    return 0;
+}
+// Camera-batch partition: every rank contributes `bytes` from d_send; the root receives rank r's block at d_recv_all + r * bytes
+// (its own block is copied device-to-device).  One grouped ncclSend/ncclRecv exchange, asynchronous on `stream`.
+int grtGatherFrames(grtContext* c, void* stream_v, const void* d_send, size_t bytes, void* d_recv_all, int root) {
+    if (!c) return 1;
+    if (!c->comm) return fail(c, "grtGatherFrames: no communicator (grtCommInit)");
+    if (root < 0 || root >= c->comm_nranks) return fail(c, "grtGatherFrames: root %d of %d", root, c->comm_nranks);
+    cudaStream_t stream = (cudaStream_t)stream_v;
+    DEV(c);
+    if (c->comm_rank == root) {
+        if (!d_recv_all) return fail(c, "grtGatherFrames: the root needs a receive buffer");
+        NC(c, g_nccl.GroupStart());
+        for (int r = 0; r < c->comm_nranks; ++r)
+            if (r != root) NC(c, g_nccl.Recv((char*)d_recv_all + (size_t)r * bytes, bytes, /*ncclUint8*/ 1, r, c->comm, stream));
+        NC(c, g_nccl.GroupEnd());
+        if (d_send && (const char*)d_send != (const char*)d_recv_all + (size_t)root * bytes)
+            CU(c, cudaMemcpyAsync((char*)d_recv_all + (size_t)root * bytes, d_send, bytes, cudaMemcpyDeviceToDevice, stream));
+    } else {
+        NC(c, g_nccl.Send(d_send, bytes, 1, root, c->comm, stream));
+    }
+    return 0;
+}
+// Row-band partition of ONE frame (grtLaunchRows with band_stride = nranks, band_offset = rank): every rank sends the bands it
+// traced straight out of its frame buffer, the root receives them in place at the same offsets of ITS frame buffer (which
+// already holds the root's own bands): no packing, one grouped exchange.
+int grtGatherBands(grtContext* c, void* stream_v, void* d_frame, uint32_t width, uint32_t height, uint32_t band_rows, int root) {
+    if (!c) return 1;
+    if (!c->comm) return fail(c, "grtGatherBands: no communicator (grtCommInit)");
+    if (!d_frame || band_rows == 0 || (band_rows & 7u)) return fail(c, "grtGatherBands: bad argument (band_rows %u)", band_rows);
+    if (root < 0 || root >= c->comm_nranks) return fail(c, "grtGatherBands: root %d of %d", root, c->comm_nranks);
+    cudaStream_t stream = (cudaStream_t)stream_v;
+    DEV(c);
+    const uint32_t n_bands = (height + band_rows - 1u) / band_rows;
+    const size_t row_bytes = (size_t)width * 3u;
+    NC(c, g_nccl.GroupStart());
+    for (uint32_t b = 0; b < n_bands; ++b) {
+        const int owner = (int)(b % (uint32_t)c->comm_nranks);
+        const uint32_t y0 = b * band_rows, rows = (y0 + band_rows <= height) ? band_rows : height - y0;
+        char* p = (char*)d_frame + (size_t)y0 * row_bytes;
+        if (c->comm_rank == root && owner != root) NC(c, g_nccl.Recv(p, rows * row_bytes, 1, owner, c->comm, stream));
+        else if (c->comm_rank != root && owner == c->comm_rank) NC(c, g_nccl.Send(p, rows * row_bytes, 1, root, c->comm, stream));
+    }
+    NC(c, g_nccl.GroupEnd());
+    return 0;
+}
+
 int grtGetAbiLayout(uint64_t out[32]) {
     if (!out) return 1;
     int k = 0;

@@ -146,6 +146,20 @@ int grtLaunchBatch(grtContext* ctx, void* stream, const grtParams* host_params_a
  * host_params->output_buffer is ignored. h == 0 means the full frame. */
 int grtRenderHost(grtContext* ctx, const grtParams* host_params, uint8_t* host_rgb8, uint32_t y0, uint32_t h);
 
+/* -- multi-GPU (the reference is single-GPU, src/GaussianTracer.h:50): the scene and its accel are replicated per GPU,
+ *    rays are partitioned (cameras k mod G, or row bands of one frame: grtLaunchRows) and the ONLY exchange is the gather of RGB8
+ *    frame data to a root rank -- grouped ncclSend/ncclRecv over NVLink, asynchronous on the caller's stream.  NCCL is bound at
+ *    run time (dlopen of libnccl.so.2); one context = one rank.  The 128-byte id comes from grtCommGetUniqueId on one rank and
+ *    reaches the others by any host channel (file, socket, MPI, torch.distributed broadcast). -- */
+int grtCommGetUniqueId(uint8_t out128[128]);
+int grtCommInit(grtContext* ctx, int nranks, int rank, const uint8_t id128[128]);
+int grtCommDestroy(grtContext* ctx);
+/* every rank: `bytes` from d_send; root: rank r's block lands at d_recv_all + r*bytes (non-roots pass NULL) */
+int grtGatherFrames(grtContext* ctx, void* stream, const void* d_send, size_t bytes, void* d_recv_all, int root);
+/* row bands of one width x height RGB8 frame: band b (band_rows rows, a multiple of 8) was traced by rank b % nranks into ITS d_frame;
+ * afterwards the root's d_frame holds the whole frame */
+int grtGatherBands(grtContext* ctx, void* stream, void* d_frame, uint32_t width, uint32_t height, uint32_t band_rows, int root);
+
 /* -- parity / profiling side channels (not in the reference; Params layout untouched) --
  * d_rgb32f: width*height*3 floats, accumColor before clamp+quantise (NULL disables).
  * Hit-ID traces for the pixel rectangle (tx0,ty0,tw,th): the first trace_max consumed particle IDs per

@@ -65,3 +65,31 @@ def test_contexts_on_two_devices_in_one_process(grt, ctx):
     finally:
         dev1.close()
         torch.cuda.set_device(0)
+
+
+@pytest.mark.parametrize("mode", ["bands", "cameras"])
+def test_nccl_gather_through_the_c_abi(grt, tmp_path, mode):
+    """One process per GPU, NO torch.distributed: row bands of one frame (grtLaunchRows + grtGatherBands) and a camera batch
+    (grtLaunch + grtGatherFrames) over libgrt's own NCCL exchange reproduce what one GPU renders alone, bit for bit."""
+    import os
+    import subprocess
+    import sys
+    world = min(_device_count(grt), 4)
+    if world < 2:
+        pytest.skip("needs >= 2 GPUs in one box (run under gpurun --gpus 2; log kept in profiles/)")
+    worker = os.path.join(os.path.dirname(os.path.abspath(__file__)), "mgpu_worker.py")
+    id_file, out = str(tmp_path / "nccl_id"), str(tmp_path / "out.npz")
+    procs = [subprocess.Popen([sys.executable, worker, str(r), str(world), id_file, out, mode], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+             for r in range(world)]
+    logs = []
+    for p in procs:
+        try:
+            logs.append(p.communicate(timeout=300)[0])
+        except subprocess.TimeoutExpired:
+            for q in procs:
+                q.kill()
+            raise
+    assert all(p.returncode == 0 for p in procs), "\n".join(logs)
+    z = np.load(out)
+    assert z["got"].shape == z["want"].shape and z["want"].max() > 0
+    assert np.array_equal(z["got"], z["want"])
