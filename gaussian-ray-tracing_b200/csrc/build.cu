@@ -915,6 +915,47 @@ __global__ void tri_gather_kernel(const float* __restrict__ tri9, const uint2* _
     out[j] = r;
 }
 
+// Reflection primitives arrive in OBJECT space with a glm 4x4 each (src/geometry/Primitives.h:14-29).  What the reference does on
+// the host per update -- the instance transform OptiX applies to the GAS vertices, and vertex_normals[i] = mat3(transform) * n
+// (src/GaussianTracer.cpp:658-663, NOT the inverse transpose) -- runs here on the device, in glm's un-fused evaluation order
+// (column by column: (T[0]*x + T[1]*y) + T[2]*z (+ T[3])), so that the bits equal the oracle's host evaluation.
+__global__ void mesh_vertices_kernel(const float* __restrict__ ov, const float* __restrict__ on, const MeshPrep* __restrict__ prep, uint32_t n_meshes,
+                                     uint32_t n_verts, float* __restrict__ vw, float* __restrict__ nw) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_verts) return;
+    uint32_t m = 0;
+    while (m + 1 < n_meshes && i >= prep[m + 1].v_off) ++m;
+    const float* T = prep[m].T;  // glm column-major: T[4*col + row]
+    const float x = ov[3 * i], y = ov[3 * i + 1], z = ov[3 * i + 2];
+    const float nx = on[3 * i], ny = on[3 * i + 1], nz = on[3 * i + 2];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+        vw[3 * i + r] = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(T[0 + r], x), __fmul_rn(T[4 + r], y)), __fmul_rn(T[8 + r], z)), T[12 + r]);
+        nw[3 * i + r] = __fadd_rn(__fadd_rn(__fmul_rn(T[0 + r], nx), __fmul_rn(T[4 + r], ny)), __fmul_rn(T[8 + r], nz));
+    }
+}
+__global__ void mesh_triangles_kernel(const float* __restrict__ vw, const uint32_t* __restrict__ idx, const MeshPrep* __restrict__ prep, uint32_t n_meshes,
+                                      uint32_t n_tris, float* __restrict__ tri9, uint2* __restrict__ meta) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_tris) return;
+    uint32_t m = 0;
+    while (m + 1 < n_meshes && t >= prep[m + 1].tri_off) ++m;
+    const uint32_t f = t - prep[m].tri_off;
+    const uint32_t* ix = idx + prep[m].i_off + 3u * f;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const float* v = vw + 3u * (prep[m].v_off + ix[c]);
+        tri9[9 * (size_t)t + 3 * c] = v[0]; tri9[9 * (size_t)t + 3 * c + 1] = v[1]; tri9[9 * (size_t)t + 3 * c + 2] = v[2];
+    }
+    meta[t] = make_uint2(m, f);
+}
+int mesh_prepare(const float* d_ov, const float* d_on, const uint32_t* d_idx, const MeshPrep* d_prep, uint32_t n_meshes, uint32_t n_verts,
+                 uint32_t n_tris, float* d_vw, float* d_nw, float* d_tri9, uint2* d_meta, cudaStream_t stream, unsigned long long* launches) {
+    if (n_verts) { mesh_vertices_kernel<<<cdiv(n_verts, 128), 128, 0, stream>>>(d_ov, d_on, d_prep, n_meshes, n_verts, d_vw, d_nw); ++*launches; }
+    if (n_tris) { mesh_triangles_kernel<<<cdiv(n_tris, 128), 128, 0, stream>>>(d_vw, d_idx, d_prep, n_meshes, n_tris, d_tri9, d_meta); ++*launches; }
+    return (int)cudaGetLastError();
+}
+
 int mesh_compute_boxes(const float* d_tri9, uint32_t n, float4* d_lo, float4* d_hi, cudaStream_t stream, unsigned long long* launches) {
     if (!n) return 0;
     tri_boxes_kernel<<<cdiv(n, 128), 128, 0, stream>>>(d_tri9, n, d_lo, d_hi);

@@ -44,10 +44,9 @@ struct grtContext {
     uint64_t particles_cap = 0;                // capacity (records) of d_particles / d_s
     bool p_valid = false;                      // the particle accel matches the resident particle set
     // meshes
-    std::vector<float> h_tri9;
-    std::vector<uint2> h_meta;
-    std::vector<std::vector<float>> h_normals;  // per mesh, transformed
-    std::vector<std::vector<uint32_t>> h_faces; // per mesh
+    std::vector<float> h_ov, h_on;              // object-space vertices / normals of all meshes, concatenated (as grtSetMeshes got them)
+    std::vector<uint32_t> h_idx;                // triangle indices of all meshes, concatenated (= the reference's Mesh.faces arrays)
+    std::vector<MeshPrep> h_prep;               // per mesh: transform and offsets; world-space data is produced on the device
     std::vector<void*> mesh_allocs;             // mesh device arrays that did not fit into mesh_pool (freed on the next build)
     BuildScratch mesh_pool;                     // faces / normals / Mesh table / triangle records / header of the current mesh accel
     uint32_t m_nodes_cap = 0;                   // capacity of m_nodes (kept across rebuilds)
@@ -527,37 +526,28 @@ int grtBuildParticleAccel(grtContext* c, void* stream_v, uint64_t* handle_out, v
 int grtSetMeshes(grtContext* c, const grtMeshDesc* meshes, uint32_t n) {
     if (!c) return 1;
     if (n && !meshes) return fail(c, "grtSetMeshes: meshes is NULL");
-    c->h_tri9.clear(); c->h_meta.clear(); c->h_normals.clear(); c->h_faces.clear();
+    // Only validation and a copy of the caller's arrays happen here; the per-vertex transform the reference host does on every
+    // update (world vertices of the instance, normals = mat3(transform) * n: src/GaussianTracer.cpp:658-663, 711-794) runs on the
+    // device in grtBuildMeshAccel.
+    c->h_ov.clear(); c->h_on.clear(); c->h_idx.clear(); c->h_prep.clear();
+    uint32_t tri_off = 0;
     for (uint32_t m = 0; m < n; ++m) {
         const grtMeshDesc& d = meshes[m];
         if (d.index_count % 3) return fail(c, "grtSetMeshes: mesh %u index_count %u is not a multiple of 3", m, d.index_count);
-        const float* T = d.transform;  // glm column-major: T[4*col + row]
-        // world vertices = what an OptiX instance transform does to the GAS vertices; normals = mat3(transform) * n,
-        // NOT inverse-transpose (src/GaussianTracer.cpp:658-663).  Un-fused, glm's evaluation order.
-        std::vector<float> vw(3ull * d.vertex_count), nw(3ull * d.vertex_count);
-        for (uint32_t i = 0; i < d.vertex_count; ++i) {
-            const float x = d.vertices[3 * i], y = d.vertices[3 * i + 1], z = d.vertices[3 * i + 2];
-            const float nx = d.normals[3 * i], ny = d.normals[3 * i + 1], nz = d.normals[3 * i + 2];
-            for (int r = 0; r < 3; ++r) {
-                volatile float a = T[0 + r] * x, b = T[4 + r] * y, cc = T[8 + r] * z;
-                volatile float s1 = a + b; volatile float s2 = s1 + cc;
-                vw[3 * i + r] = s2 + T[12 + r];
-                volatile float na = T[0 + r] * nx, nb = T[4 + r] * ny, nc = T[8 + r] * nz;
-                volatile float n1 = na + nb;
-                nw[3 * i + r] = n1 + nc;
+        if ((d.vertex_count && (!d.vertices || !d.normals)) || (d.index_count && !d.indices)) return fail(c, "grtSetMeshes: mesh %u has a NULL array", m);
+        for (uint32_t k = 0; k < d.index_count; ++k)
+            if (d.indices[k] >= d.vertex_count) {
+                c->h_ov.clear(); c->h_on.clear(); c->h_idx.clear(); c->h_prep.clear();
+                return fail(c, "grtSetMeshes: mesh %u face %u references vertex %u >= %u", m, k / 3, d.indices[k], d.vertex_count);
             }
-        }
-        std::vector<uint32_t> faces(d.indices, d.indices + d.index_count);
-        for (uint32_t f = 0; f < d.index_count / 3; ++f) {
-            for (int j = 0; j < 3; ++j) {
-                const uint32_t vi = faces[3 * f + j];
-                if (vi >= d.vertex_count) return fail(c, "grtSetMeshes: mesh %u face %u references vertex %u >= %u", m, f, vi, d.vertex_count);
-                c->h_tri9.push_back(vw[3 * vi]); c->h_tri9.push_back(vw[3 * vi + 1]); c->h_tri9.push_back(vw[3 * vi + 2]);
-            }
-            c->h_meta.push_back(make_uint2(m, f));
-        }
-        c->h_normals.push_back(std::move(nw));
-        c->h_faces.push_back(std::move(faces));
+        MeshPrep p{};
+        memcpy(p.T, d.transform, sizeof(p.T));
+        p.v_off = (uint32_t)(c->h_ov.size() / 3); p.i_off = (uint32_t)c->h_idx.size(); p.tri_off = tri_off;
+        c->h_ov.insert(c->h_ov.end(), d.vertices, d.vertices + 3ull * d.vertex_count);
+        c->h_on.insert(c->h_on.end(), d.normals, d.normals + 3ull * d.vertex_count);
+        c->h_idx.insert(c->h_idx.end(), d.indices, d.indices + d.index_count);
+        tri_off += d.index_count / 3;
+        c->h_prep.push_back(p);
     }
     return 0;
 }
@@ -573,8 +563,8 @@ int grtBuildMeshAccel(grtContext* c, void* stream_v, uint64_t* mesh_handle_out, 
     if (mesh_handle_out) *mesh_handle_out = 0;
     if (d_meshes_out) *d_meshes_out = nullptr;
     c->info.n_mesh_triangles = 0; c->info.n_mesh_wide_nodes = 0; c->info.mesh_build_ms = 0;
-    const uint32_t nm = (uint32_t)c->h_faces.size();
-    const uint32_t nt = (uint32_t)c->h_meta.size();
+    const uint32_t nm = (uint32_t)c->h_prep.size();
+    const uint32_t nv = (uint32_t)(c->h_ov.size() / 3), ni = (uint32_t)c->h_idx.size(), nt = ni / 3;
     if (nm == 0) return 0;
     // Moving a primitive rebuilds this accel every frame (updateInstanceTransforms, src/GaussianTracer.cpp:711-794): the
     // persistent arrays come from a pool that is kept between builds, the temporaries from the build scratch block.
@@ -586,42 +576,48 @@ int grtBuildMeshAccel(grtContext* c, void* stream_v, uint64_t* mesh_handle_out, 
         if (e == cudaSuccess) c->mesh_allocs.push_back(*out);
         return e;
     };
-    // Mesh{faces, vertex_normals}[] exactly as sendGeometryAttributesToDevice builds it (src/GaussianTracer.cpp:653-709)
-    std::vector<MeshDev> hm(nm);
-    for (uint32_t m = 0; m < nm; ++m) {
-        void *df = nullptr, *dn = nullptr;
-        CU(c, palloc(c->h_faces[m].size() * 4, &df));
-        CU(c, palloc(c->h_normals[m].size() * 4, &dn));
-        CU(c, cudaMemcpyAsync(df, c->h_faces[m].data(), c->h_faces[m].size() * 4, cudaMemcpyHostToDevice, stream));
-        CU(c, cudaMemcpyAsync(dn, c->h_normals[m].data(), c->h_normals[m].size() * 4, cudaMemcpyHostToDevice, stream));
-        hm[m].faces = (uint3*)df;
-        hm[m].vertex_normals = (float3*)dn;
-    }
-    { void* p = nullptr; CU(c, palloc(sizeof(MeshDev) * nm, &p)); c->d_meshes = (MeshDev*)p; }
-    CU(c, cudaMemcpyAsync(c->d_meshes, hm.data(), sizeof(MeshDev) * nm, cudaMemcpyHostToDevice, stream));
-    if (d_meshes_out) *d_meshes_out = c->d_meshes;
-    if (nt == 0) { CU(c, cudaStreamSynchronize(stream)); return 0; }
     if (!c->ev_b0) { CU(c, cudaEventCreate(&c->ev_b0)); CU(c, cudaEventCreate(&c->ev_b1)); }
     CU(c, cudaEventRecord(c->ev_b0, stream));
+    // persistent: Mesh{faces, vertex_normals}[] exactly as sendGeometryAttributesToDevice leaves it (src/GaussianTracer.cpp:653-709):
+    // faces = the index triples, vertex_normals = mat3(transform) * normal
+    uint32_t* d_idx = nullptr; float* d_nw = nullptr;
+    { void* p = nullptr; CU(c, palloc(sizeof(uint32_t) * (size_t)ni, &p)); d_idx = (uint32_t*)p; }
+    { void* p = nullptr; CU(c, palloc(sizeof(float) * 3ull * nv, &p)); d_nw = (float*)p; }
+    { void* p = nullptr; CU(c, palloc(sizeof(MeshDev) * nm, &p)); c->d_meshes = (MeshDev*)p; }
+    std::vector<MeshDev> hm(nm);
+    for (uint32_t m = 0; m < nm; ++m) {
+        hm[m].faces = (uint3*)(d_idx + c->h_prep[m].i_off);
+        hm[m].vertex_normals = (float3*)(d_nw + 3ull * c->h_prep[m].v_off);
+    }
+    CU(c, cudaMemcpyAsync(d_idx, c->h_idx.data(), sizeof(uint32_t) * (size_t)ni, cudaMemcpyHostToDevice, stream));
+    CU(c, cudaMemcpyAsync(c->d_meshes, hm.data(), sizeof(MeshDev) * nm, cudaMemcpyHostToDevice, stream));
+    if (d_meshes_out) *d_meshes_out = c->d_meshes;
     c->scratch.begin();
     struct Tmp {  // scratch block, else cudaMalloc'd for this build only
         void* p = nullptr; bool owned = false;
         ~Tmp() { if (owned) cudaFree(p); }
         cudaError_t alloc(BuildScratch& s, size_t bytes) {
-            p = s.get(bytes);
+            p = s.get(bytes ? bytes : 4);
             if (p) return cudaSuccess;
             owned = true;
-            return cudaMalloc(&p, bytes);
+            return cudaMalloc(&p, bytes ? bytes : 4);
         }
-    } t_tri9, t_meta, t_lo, t_hi;
+    } t_ov, t_on, t_vw, t_prep, t_tri9, t_meta, t_lo, t_hi;
+    CU(c, t_ov.alloc(c->scratch, sizeof(float) * 3ull * nv));
+    CU(c, t_on.alloc(c->scratch, sizeof(float) * 3ull * nv));
+    CU(c, t_vw.alloc(c->scratch, sizeof(float) * 3ull * nv));
+    CU(c, t_prep.alloc(c->scratch, sizeof(MeshPrep) * (size_t)nm));
     CU(c, t_tri9.alloc(c->scratch, sizeof(float) * 9ull * nt));
     CU(c, t_meta.alloc(c->scratch, sizeof(uint2) * (size_t)nt));
     CU(c, t_lo.alloc(c->scratch, sizeof(float4) * (size_t)nt));
     CU(c, t_hi.alloc(c->scratch, sizeof(float4) * (size_t)nt));
     float* d_tri9 = (float*)t_tri9.p; uint2* d_meta = (uint2*)t_meta.p; float4 *d_lo = (float4*)t_lo.p, *d_hi = (float4*)t_hi.p;
-    CU(c, cudaMemcpyAsync(d_tri9, c->h_tri9.data(), sizeof(float) * 9ull * nt, cudaMemcpyHostToDevice, stream));
-    CU(c, cudaMemcpyAsync(d_meta, c->h_meta.data(), sizeof(uint2) * (size_t)nt, cudaMemcpyHostToDevice, stream));
-    int rc = mesh_compute_boxes(d_tri9, nt, d_lo, d_hi, stream, &c->launches);
+    CU(c, cudaMemcpyAsync(t_ov.p, c->h_ov.data(), sizeof(float) * 3ull * nv, cudaMemcpyHostToDevice, stream));
+    CU(c, cudaMemcpyAsync(t_on.p, c->h_on.data(), sizeof(float) * 3ull * nv, cudaMemcpyHostToDevice, stream));
+    CU(c, cudaMemcpyAsync(t_prep.p, c->h_prep.data(), sizeof(MeshPrep) * (size_t)nm, cudaMemcpyHostToDevice, stream));
+    int rc = mesh_prepare((const float*)t_ov.p, (const float*)t_on.p, d_idx, (const MeshPrep*)t_prep.p, nm, nv, nt, (float*)t_vw.p, d_nw, d_tri9, d_meta, stream, &c->launches);
+    if (!rc && nt == 0) { CU(c, cudaStreamSynchronize(stream)); return 0; }
+    if (!rc) rc = mesh_compute_boxes(d_tri9, nt, d_lo, d_hi, stream, &c->launches);
     LbvhResult res;
     res.reuse_nodes = c->m_nodes;
     res.reuse_cap = c->m_nodes_cap;

@@ -132,6 +132,14 @@ struct PlyLayout {
 };
 int particles_activate(const unsigned char* d_rows, const PlyLayout& L, uint32_t n, float alpha_min, float* d_out59, float* d_s,
                        cudaStream_t stream, unsigned long long* launches);
+// object-space primitives -> world-space triangle soup + transformed normals on the device (build.cu)
+struct MeshPrep {
+    float T[16];            // glm column-major 4x4
+    uint32_t v_off, i_off;  // first vertex / first index of this mesh in the concatenated arrays
+    uint32_t tri_off, pad;  // first triangle
+};
+int mesh_prepare(const float* d_ov, const float* d_on, const uint32_t* d_idx, const MeshPrep* d_prep, uint32_t n_meshes, uint32_t n_verts,
+                 uint32_t n_tris, float* d_vw, float* d_nw, float* d_tri9, uint2* d_meta, cudaStream_t stream, unsigned long long* launches);
 // triangle soup: d_tri9 = n x 9 floats (world-space v0,v1,v2), d_meta = n x (mesh, face)
 int mesh_compute_boxes(const float* d_tri9, uint32_t n_tris, float4* d_lo, float4* d_hi, cudaStream_t stream,
                        unsigned long long* launches);
