@@ -238,10 +238,11 @@ def main():
     sampler.stop_flag = True
     sampler.join(timeout=3)
     total_ms = span_ms - flush_ms           # the flush writes sit between the frames on the same stream; they are not part of a step
+    kernel_ms_max_rank = float(np.mean(kernel_ms))
     if world > 1:
-        t = torch.tensor([total_ms], device="cuda")
+        t = torch.tensor([total_ms, kernel_ms_max_rank], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms = float(t.item())
+        total_ms, kernel_ms_max_rank = float(t[0].item()), float(t[1].item())
     launches = ctx.counters()["kernel_launches"] - launches_before
     value = world * rays * args.steps / (total_ms * 1e-3) / 1e6
     last = (args.steps - 1) & 1
@@ -312,7 +313,7 @@ def main():
                                      "on a side stream under the next frame's kernel") if world > 1 else "single GPU",
                        "timing": "span from the first frame's kernel start to the last gather's end, minus the L2-flush writes between frames; max over ranks",
                        "hits_gathered_per_ray": hg, "hits_shaded_per_ray": hs, "rounds_per_ray": cnt["rounds"] / cnt["rays"]},
-            "kernel_ms": k_ms,
+            "kernel_ms": k_ms, "kernel_ms_max_rank": kernel_ms_max_rank,   # rank 0's camera / the most expensive camera of the ring
             "e2e": {"value": e2e, "unit": "Mrays/s", "h2d_bytes_per_step": 144, "d2h_bytes_per_step": rays * 3},
             "gpu_launches": int(launches),
             "clocks": sampler.result(),

@@ -8,6 +8,6 @@ ARCH="-gencode arch=compute_100a,code=sm_100a"
 while [ $# -ge 2 ]; do
   name=$1; flags=$2; shift 2
   (nvcc $ARCH -lineinfo -O3 -std=c++17 -Xcompiler -fPIC $flags -c trace.cu -o variants/trace_$name.o && \
-   nvcc $ARCH -shared -o variants/libgrt_$name.so capi.o build.o ingest.o variants/trace_$name.o && rm variants/trace_$name.o && echo built $name) &
+   nvcc $ARCH -shared -o variants/libgrt_$name.so capi.o build.o ingest.o variants/trace_$name.o -ldl && rm variants/trace_$name.o && echo built $name) &
 done
 wait
