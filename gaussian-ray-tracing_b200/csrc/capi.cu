@@ -859,6 +859,7 @@ int grtGetCounters(grtContext* c, grtCounters* out, int reset) {
     out->order_violations = d.order_violations; out->warp_dfs_fallbacks = d.warp_dfs_fallbacks; out->warp_candidate_iters = d.warp_candidate_iters;
     for (int k = 0; k < 8; ++k) out->dbg[k] = d.dbg[k];
     out->warp_per_ray_passes = d.warp_per_ray_passes;
+    out->warp_composite_rounds = d.warp_composite_rounds; out->warp_loop_iters = d.warp_loop_iters;
     if (reset) CU(c, cudaMemset(c->d_counters, 0, sizeof(DeviceCounters)));
     return 0;
 }

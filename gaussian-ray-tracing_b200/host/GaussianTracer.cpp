@@ -65,8 +65,14 @@ void GaussianTracer::initializeOptix() {
 void GaussianTracer::render(CUDAOutputBuffer& output_buffer) { renderTile(output_buffer, 0, 0, params.width, params.height); }
 
 void GaussianTracer::renderTile(CUDAOutputBuffer& output_buffer, unsigned x0, unsigned y0, unsigned w, unsigned h) {
-    if (params.mode_fisheye) {  // GaussianTracer.cpp:510-513
-        GRT_CHECK(m_ctx, grtMemset(m_ctx, output_buffer.map(), 0, (size_t)params.width * params.height * sizeof(uchar3), stream));
+    if (params.mode_fisheye && w != 0 && h != 0) {  // GaussianTracer.cpp:510-513 clears the frame; a tile clears only its own rows
+        unsigned char* base = reinterpret_cast<unsigned char*>(output_buffer.map());
+        if (x0 == 0 && w == params.width) {
+            GRT_CHECK(m_ctx, grtMemset(m_ctx, base + (size_t)y0 * params.width * sizeof(uchar3), 0, (size_t)h * params.width * sizeof(uchar3), stream));
+        } else {
+            for (unsigned y = y0; y < y0 + h; ++y)
+                GRT_CHECK(m_ctx, grtMemset(m_ctx, base + ((size_t)y * params.width + x0) * sizeof(uchar3), 0, (size_t)w * sizeof(uchar3), stream));
+        }
         output_buffer.unmap();
     }
     params.output_buffer = output_buffer.map();

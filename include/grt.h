@@ -90,6 +90,8 @@ typedef struct grtCounters {
     uint64_t warp_candidate_iters; /* warp iterations of the per-ray exact proxy test loop */
     uint64_t dbg[8];          /* free-form profiling counters of the counting kernel variant (meaning: DESIGN.md) */
     uint64_t warp_per_ray_passes; /* traversal passes that ran ray by ray (divergent secondary packets, trace_rays_dfs) */
+    uint64_t warp_composite_rounds; /* compositing rounds (work list + shade + accumulate), per warp */
+    uint64_t warp_loop_iters;  /* iterations of the traversal loop, per warp */
 } grtCounters;
 
 typedef struct grtContext grtContext;
