@@ -98,7 +98,7 @@ GRT_SYMBOLS = [
     "grtBuildMeshAccel", "grtLaunch", "grtLaunchTile", "grtLaunchBatch", "grtRenderHost", "grtSetDebugOutputs",
     "grtEnableCounters", "grtGetCounters", "grtGetBuildInfo", "grtValidateAccel", "grtLastLaunchMs", "grtMalloc",
     "grtFree", "grtMallocHost", "grtFreeHost", "grtMemcpyDtoH", "grtMemcpyHtoD", "grtMemset", "grtStreamCreate",
-    "grtStreamDestroy", "grtStreamSynchronize", "grtDebugRadixSort", "grtSetParticlesRaw", "grtLoadPly", "grtGetParticles",
+    "grtStreamDestroy", "grtStreamSynchronize", "grtDebugRadixSort", "grtSortPairsNoAlloc", "grtSetParticlesRaw", "grtLoadPly", "grtGetParticles",
     "grtLaunchRows", "grtGetAbiLayout", "grtCommGetUniqueId", "grtCommInit", "grtCommDestroy", "grtGatherFrames", "grtGatherBands",
 ]
 
@@ -143,6 +143,7 @@ def load_libgrt():
         "grtStreamDestroy": [vp, vp],
         "grtStreamSynchronize": [vp, vp],
         "grtDebugRadixSort": [vp, vp, vp, u64],
+        "grtSortPairsNoAlloc": [vp, vp, vp, u64, vp],
         "grtSetParticlesRaw": [vp, vp, u64, u32, C.POINTER(u32), f32],
         "grtLoadPly": [vp, C.c_char_p, f32, C.POINTER(u64), C.POINTER(f32)],
         "grtGetParticles": [vp, vp, u64],
@@ -366,6 +367,10 @@ class Context:
         vals = np.ascontiguousarray(vals, dtype=np.uint32).copy()
         self._ck(self.lib.grtDebugRadixSort(self.h, _np_ptr(keys), _np_ptr(vals), keys.shape[0]))
         return keys, vals
+
+    def sort_pairs_noalloc(self, d_keys: int, d_vals: int, n: int, stream=None):
+        """In-place device sort of n (uint64 key, uint32 value) pairs through the allocation-free entry point."""
+        self._ck(self.lib.grtSortPairsNoAlloc(self.h, d_keys, d_vals, n, stream))
 
 
 from .scene import (  # noqa: E402

@@ -15,6 +15,8 @@
 #include <utility>
 #include <vector>
 
+#include <mutex>
+
 #include "grt_internal.h"
 
 namespace grt {
@@ -239,6 +241,64 @@ int radix_sort_pairs(uint64_t* d_keys, uint64_t* d_keys_tmp, uint32_t* d_vals, u
     CK(cudaGetLastError());
     return 0;
 }
+
+// ------------------------------------------------------------------------------------------- allocation-free sort
+// The same eight LSD passes as radix_sort_pairs, for callers that must not allocate (CUDA graph capture, serving loops): the
+// ping-pong key / value buffers and the histograms live in ONE file-scope device array instead of cudaMalloc'd or BuildScratch
+// memory.  Every GPU that loads the library holds the array until the process exits; every call shares it (calls that overlap
+// on the GPU race) and it keeps the last call's contents -- the digit totals, the only part that has to start at zero, are
+// cleared by each call.
+constexpr uint32_t NOALLOC_SORT_MAX_N = GRT_NOALLOC_SORT_MAX_N;
+constexpr size_t NA_KEYS_OFF = 0;
+constexpr size_t NA_VALS_OFF = NA_KEYS_OFF + sizeof(uint64_t) * (size_t)NOALLOC_SORT_MAX_N;
+constexpr size_t NA_HIST_OFF = NA_VALS_OFF + sizeof(uint32_t) * (size_t)NOALLOC_SORT_MAX_N;
+constexpr size_t NA_HIST_BYTES = sizeof(uint32_t) * (256ull * ((NOALLOC_SORT_MAX_N + RS_TILE - 1) / RS_TILE) + 8ull * 256ull);
+constexpr size_t NA_TOTAL = NA_HIST_OFF + NA_HIST_BYTES;   // 12.5 MiB + 520 KiB at 2^20 pairs
+static_assert(NA_VALS_OFF % 256 == 0 && NA_HIST_OFF % 256 == 0, "sub-buffers stay 256-byte aligned");
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NA_TOTAL];
+
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol, not a device address: the address is looked up once per
+// device, with that device current, and cached.
+constexpr int NA_MAX_DEVICES = 64;
+static std::mutex g_noalloc_mu;
+static unsigned char* g_noalloc_ptr[NA_MAX_DEVICES] = {};
+
+int radix_sort_pairs_noalloc(int device, uint64_t* d_keys, uint32_t* d_vals, uint32_t n, cudaStream_t stream, unsigned long long* launches) {
+    if (n == 0) return 0;
+    if (n > NOALLOC_SORT_MAX_N || device < 0 || device >= NA_MAX_DEVICES) return (int)cudaErrorInvalidValue;  // (the caller words the error)
+    unsigned char* base = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(g_noalloc_mu);
+        if (!g_noalloc_ptr[device]) {
+            CK(cudaSetDevice(device));
+            void* p = nullptr;
+            CK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+            g_noalloc_ptr[device] = static_cast<unsigned char*>(p);
+        }
+        base = g_noalloc_ptr[device];
+    }
+    uint64_t* k_tmp = reinterpret_cast<uint64_t*>(base + NA_KEYS_OFF);
+    uint32_t* v_tmp = reinterpret_cast<uint32_t*>(base + NA_VALS_OFF);
+    uint32_t* d_hist = reinterpret_cast<uint32_t*>(base + NA_HIST_OFF);
+    const uint32_t nblocks = cdiv(n, RS_TILE);
+    uint32_t* d_tot = d_hist + 256ull * nblocks;
+    CK(cudaMemsetAsync(d_tot, 0, sizeof(uint32_t) * 8 * 256, stream));   // the digit totals are accumulated with atomics
+    uint64_t* kin = d_keys; uint64_t* kout = k_tmp;
+    uint32_t* vin = d_vals; uint32_t* vout = v_tmp;
+    for (int pass = 0; pass < 8; ++pass) {
+        const int shift = pass * 8;
+        rs_hist_kernel<<<nblocks, RS_THREADS, 0, stream>>>(kin, n, shift, d_hist, d_tot + 256 * pass, nblocks);
+        rs_scan_kernel<<<256 / RS_WARPS, RS_THREADS, 0, stream>>>(d_hist, d_tot + 256 * pass, nblocks);
+        rs_scatter_kernel<<<nblocks, RS_THREADS, 0, stream>>>(kin, vin, kout, vout, n, shift, d_hist, nblocks);
+        *launches += 3;
+        std::swap(kin, kout);
+        std::swap(vin, vout);
+    }
+    // 8 passes: the result is back in the caller's buffers
+    CK(cudaGetLastError());
+    return 0;
+}
+uint32_t radix_sort_pairs_noalloc_max() { return NOALLOC_SORT_MAX_N; }
 
 // ------------------------------------------------------------------------------------------- bounds + Morton
 __device__ __forceinline__ uint32_t enc_f(float f) {

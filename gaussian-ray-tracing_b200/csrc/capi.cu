@@ -959,4 +959,19 @@ int grtDebugRadixSort(grtContext* c, uint64_t* host_keys, uint32_t* host_vals, u
     return 0;
 }
 
+// No counterpart in the reference (see include/grt.h).
+int grtSortPairsNoAlloc(grtContext* c, uint64_t* d_keys, uint32_t* d_vals, uint64_t n, void* stream) {
+    if (!c) return 1;
+    if (n == 0) return 0;
+    if (!d_keys || !d_vals) return fail(c, "grtSortPairsNoAlloc: null device pointer");
+    const uint32_t max_n = radix_sort_pairs_noalloc_max();
+    if (n > max_n)
+        return fail(c, "grtSortPairsNoAlloc: n = %llu exceeds the static scratch array's maximum of %u pairs (GRT_NOALLOC_SORT_MAX_N)",
+                    (unsigned long long)n, max_n);
+    DEV(c);
+    const int rc = radix_sort_pairs_noalloc(c->device, d_keys, d_vals, (uint32_t)n, (cudaStream_t)stream, &c->launches);
+    if (rc) return fail(c, "grtSortPairsNoAlloc failed: %s", cudaGetErrorString((cudaError_t)rc));
+    return 0;
+}
+
 }  // extern "C"

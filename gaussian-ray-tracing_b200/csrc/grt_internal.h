@@ -119,6 +119,14 @@ int lbvh_build(const float4* d_lo, const float4* d_hi, uint32_t n, cudaStream_t 
 int radix_sort_pairs(uint64_t* d_keys, uint64_t* d_keys_tmp, uint32_t* d_vals, uint32_t* d_vals_tmp, uint32_t n,
                      cudaStream_t stream, unsigned long long* launches, bool* result_in_tmp, BuildScratch* scratch = nullptr);
 
+// The same sort without any allocation: temporaries in a file-scope device array of build.cu (at most GRT_NOALLOC_SORT_MAX_N pairs;
+// in place; calls that overlap on one GPU race on the array).
+#ifndef GRT_NOALLOC_SORT_MAX_N
+#define GRT_NOALLOC_SORT_MAX_N (1u << 20)
+#endif
+int radix_sort_pairs_noalloc(int device, uint64_t* d_keys, uint32_t* d_vals, uint32_t n, cudaStream_t stream, unsigned long long* launches);
+uint32_t radix_sort_pairs_noalloc_max();
+
 // particle pack kernels (build.cu)
 int particles_compute_boxes(const void* d_particles236, const float* d_s, uint32_t n, float4* d_lo, float4* d_hi,
                             cudaStream_t stream, unsigned long long* launches);

@@ -196,6 +196,16 @@ int grtStreamSynchronize(grtContext* ctx, void* stream);
 /* Sorts n (key,value) pairs with the hand-written device radix sort used by the LBVH build (test hook). */
 int grtDebugRadixSort(grtContext* ctx, uint64_t* host_keys, uint32_t* host_vals, uint64_t n);
 
+/* Allocation-free variant of the (key, value) radix sort above.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops).
+ * Sorts n pairs IN PLACE in the caller's device buffers d_keys[n] (uint64) / d_vals[n] (uint32), stable, asynchronously on
+ * `stream`.  The sort's temporaries (ping-pong buffers, histograms) live in a file-scope device array of the library
+ * (13.1 MB, held by every GPU that loads the library until exit), so n is limited to GRT_NOALLOC_SORT_MAX_N = 1 048 576
+ * pairs: a larger n is rejected with an error.  Calls no cudaMalloc / cudaFree.  All calls on one GPU share the array:
+ * calls that overlap on the GPU (different streams) race; back-to-back calls on one stream are fine. */
+#define GRT_NOALLOC_SORT_MAX_N (1u << 20)
+int grtSortPairsNoAlloc(grtContext* ctx, uint64_t* d_keys, uint32_t* d_vals, uint64_t n, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
