@@ -89,7 +89,8 @@ class GrtCounters(C.Structure):
         "rays", "segments", "rounds", "hits_gathered", "hits_shaded", "warp_nodes", "warp_leaf_prims",
         "warp_rounds", "stack_overflow", "kernel_launches", "warp_prims_hit", "warp_consume_iters", "lanes_repass",
         "order_violations", "warp_dfs_fallbacks", "warp_candidate_iters")] + [("dbg", C.c_uint64 * 8), ("warp_per_ray_passes", C.c_uint64),
-                                                       ("warp_composite_rounds", C.c_uint64), ("warp_loop_iters", C.c_uint64)]
+                                                       ("warp_composite_rounds", C.c_uint64), ("warp_loop_iters", C.c_uint64),
+                                                       ("warp_forced_flushes", C.c_uint64), ("warp_list_full", C.c_uint64)]
 
 
 # every symbol include/grt.h declares (tests check that the .so exports all of them)

@@ -860,6 +860,7 @@ int grtGetCounters(grtContext* c, grtCounters* out, int reset) {
     for (int k = 0; k < 8; ++k) out->dbg[k] = d.dbg[k];
     out->warp_per_ray_passes = d.warp_per_ray_passes;
     out->warp_composite_rounds = d.warp_composite_rounds; out->warp_loop_iters = d.warp_loop_iters;
+    out->warp_forced_flushes = d.warp_forced_flushes; out->warp_list_full = d.warp_list_full;
     if (reset) CU(c, cudaMemset(c->d_counters, 0, sizeof(DeviceCounters)));
     return 0;
 }

@@ -65,7 +65,7 @@ struct DeviceCounters {
     unsigned long long rays, segments, rounds, hits_gathered, hits_shaded, warp_nodes, warp_leaf_prims, warp_rounds,
         stack_overflow, warp_prims_hit, warp_consume_iters, lanes_repass, order_violations, warp_dfs_fallbacks, warp_candidate_iters;
     unsigned long long dbg[8];  // free-form experiment counters (tools/prof_trace.py prints them)
-    unsigned long long warp_per_ray_passes, warp_composite_rounds, warp_loop_iters;
+    unsigned long long warp_per_ray_passes, warp_composite_rounds, warp_loop_iters, warp_forced_flushes, warp_list_full;
 };
 
 // Extra kernel arguments next to the 144-byte Params.

@@ -92,6 +92,8 @@ typedef struct grtCounters {
     uint64_t warp_per_ray_passes; /* traversal passes that ran ray by ray (divergent secondary packets, trace_rays_dfs) */
     uint64_t warp_composite_rounds; /* compositing rounds (work list + shade + accumulate), per warp */
     uint64_t warp_loop_iters;  /* iterations of the traversal loop, per warp */
+    uint64_t warp_forced_flushes; /* flushes that intersected waiting slots behind the frontier because the slots ran out */
+    uint64_t warp_list_full;   /* record pops that left records in front of the nearest node behind (new-record list full) */
 } grtCounters;
 
 typedef struct grtContext grtContext;

@@ -69,7 +69,7 @@ def main():
         out["per_ray"] = {k: c[k] / rays for k in ("segments", "rounds", "hits_gathered", "hits_shaded")}
         warps = rays / 32
         out["per_warp"] = {k: c[k] / warps for k in ("warp_nodes", "warp_leaf_prims", "warp_rounds", "warp_prims_hit", "warp_consume_iters",
-                                                       "warp_candidate_iters", "warp_composite_rounds", "warp_loop_iters")}
+                                                       "warp_candidate_iters", "warp_composite_rounds", "warp_loop_iters", "warp_forced_flushes", "warp_list_full")}
         d = c.get("dbg", [0] * 8)
         out["per_ray"].update({"inserts": d[0] / rays, "shift_steps": d[1] / rays, "ring_cnt_at_insert": d[2] / max(d[0], 1),
                                "candidates": d[3] / rays, "proxy_hits": d[4] / rays, "spills": d[5] / rays})
