@@ -90,7 +90,7 @@ class GrtCounters(C.Structure):
         "warp_rounds", "stack_overflow", "kernel_launches", "warp_prims_hit", "warp_consume_iters", "lanes_repass",
         "order_violations", "warp_dfs_fallbacks", "warp_candidate_iters")] + [("dbg", C.c_uint64 * 8), ("warp_per_ray_passes", C.c_uint64),
                                                        ("warp_composite_rounds", C.c_uint64), ("warp_loop_iters", C.c_uint64),
-                                                       ("warp_forced_flushes", C.c_uint64), ("warp_list_full", C.c_uint64)]
+                                                       ("warp_forced_flushes", C.c_uint64), ("warp_dfs_iters", C.c_uint64), ("warp_list_full", C.c_uint64)]
 
 
 # every symbol include/grt.h declares (tests check that the .so exports all of them)
@@ -99,7 +99,7 @@ GRT_SYMBOLS = [
     "grtBuildMeshAccel", "grtLaunch", "grtLaunchTile", "grtLaunchBatch", "grtRenderHost", "grtSetDebugOutputs",
     "grtEnableCounters", "grtGetCounters", "grtGetBuildInfo", "grtValidateAccel", "grtLastLaunchMs", "grtMalloc",
     "grtFree", "grtMallocHost", "grtFreeHost", "grtMemcpyDtoH", "grtMemcpyHtoD", "grtMemset", "grtStreamCreate",
-    "grtStreamDestroy", "grtStreamSynchronize", "grtDebugRadixSort", "grtSortPairsNoAlloc", "grtSetParticlesRaw", "grtLoadPly", "grtGetParticles",
+    "grtStreamDestroy", "grtStreamSynchronize", "grtDebugRadixSort", "grtSortPairsNoAlloc", "grtSetWavefront", "grtSetParticlesRaw", "grtLoadPly", "grtGetParticles",
     "grtLaunchRows", "grtGetAbiLayout", "grtCommGetUniqueId", "grtCommInit", "grtCommDestroy", "grtGatherFrames", "grtGatherBands",
 ]
 
@@ -129,6 +129,7 @@ def load_libgrt():
         "grtRenderHost": [vp, C.POINTER(GrtParams), vp, u32, u32],
         "grtSetDebugOutputs": [vp, vp, vp, vp, u32, u32, u32, u32, u32],
         "grtEnableCounters": [vp, i32],
+        "grtSetWavefront": [vp, i32],
         "grtGetCounters": [vp, C.POINTER(GrtCounters), i32],
         "grtGetBuildInfo": [vp, C.POINTER(GrtBuildInfo)],
         "grtValidateAccel": [vp, i32],
@@ -336,6 +337,9 @@ class Context:
     # ---- side channels
     def set_debug_outputs(self, d_rgb32f=None, d_trace_ids=None, d_trace_counts=None, rect=(0, 0, 0, 0), trace_max=0):
         self._ck(self.lib.grtSetDebugOutputs(self.h, d_rgb32f, d_trace_ids, d_trace_counts, *rect, trace_max))
+
+    def set_wavefront(self, on: bool):
+        self._ck(self.lib.grtSetWavefront(self.h, int(on)))
 
     def enable_counters(self, on: bool):
         self._ck(self.lib.grtEnableCounters(self.h, int(on)))

@@ -4,6 +4,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -64,6 +65,8 @@ struct grtContext {
     DeviceCounters* d_counters = nullptr;
     uint32_t* d_tile_counter = nullptr;  // TILE_RING x TILE_SLOT_WORDS: one scheduler counter block per launch in flight
     uint32_t tile_seq = 0;
+    WavefrontBuffers wf;                 // wavefront mode of scenes with primitives (trace.cu), grown on demand
+    bool wavefront = true;               // grtSetWavefront; GRT_WAVEFRONT=0 in the environment turns it off at grtCreate
     bool smem_attr_set = false;          // cudaFuncAttributeMaxDynamicSharedMemorySize is per DEVICE: kept per context, not per process
     BuildScratch scratch;  // builder temporaries, kept between builds
     int sm_count = 0;
@@ -195,6 +198,7 @@ int grtCreate(int device, grtContext** ctx_out) {
     if (prop.major < 10) return fail(nullptr, "grtCreate: device %d is sm_%d%d; libgrt is built for sm_100a only", device, prop.major, prop.minor);
     grtContext* c = new grtContext();
     c->device = device;
+    { const char* e = getenv("GRT_WAVEFRONT"); if (e && e[0] == '0') c->wavefront = false; }
     c->sm_count = prop.multiProcessorCount;
     if (cudaMalloc(&c->d_tile_counter, TILE_RING * TILE_SLOT_WORDS * sizeof(uint32_t)) != cudaSuccess || cudaMalloc(&c->d_counters, sizeof(DeviceCounters)) != cudaSuccess || cudaMemset(c->d_counters, 0, sizeof(DeviceCounters)) != cudaSuccess ||
         cudaStreamCreate(&c->own_stream) != cudaSuccess || cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess) {
@@ -212,6 +216,7 @@ int grtDestroy(grtContext* c) {
     free_particle_accel(c);
     free_mesh_accel(c);
     cudaFree(c->d_particles); cudaFree(c->d_s); cudaFree(c->d_counters); cudaFree(c->d_tile_counter); cudaFree(c->d_frame);
+    cudaFree(c->wf.state); cudaFree(c->wf.list[0]); cudaFree(c->wf.list[1]); cudaFree(c->wf.ctrl);
     c->scratch.release();
     c->mesh_pool.release();
     cudaFree(c->m_nodes);
@@ -688,11 +693,27 @@ static int do_launch(grtContext* c, cudaStream_t stream, const grtParams* p, uin
     // different streams (tiles or cameras overlapped on one GPU) must not share a tile counter.
     ex.tile_counter = c->d_tile_counter + (size_t)(c->tile_seq++ % TILE_RING) * TILE_SLOT_WORDS;
     CU(c, cudaMemsetAsync(ex.tile_counter, 0, (GRT_SM_REGIONS_HOST ? TILE_SLOT_WORDS : 1u) * sizeof(uint32_t), stream));
+    const WavefrontBuffers* wf = nullptr;
+    if (ex.m_count != 0u && c->wavefront) {
+        // wavefront buffers: payload of every pixel of the rectangle + two tile lists, kept between launches, grown when a larger
+        // rectangle comes (no allocation on the steady-state path)
+        const size_t sb = wavefront_state_bytes(ex), lb = wavefront_list_bytes(ex);
+        if (sb > c->wf.state_bytes || lb > c->wf.list_bytes || !c->wf.ctrl) {
+            CU(c, cudaStreamSynchronize(stream));
+            cudaFree(c->wf.state); cudaFree(c->wf.list[0]); cudaFree(c->wf.list[1]);
+            c->wf.state = nullptr; c->wf.list[0] = c->wf.list[1] = nullptr; c->wf.state_bytes = c->wf.list_bytes = 0;
+            CU(c, cudaMalloc(&c->wf.state, sb));
+            CU(c, cudaMalloc(&c->wf.list[0], lb));
+            CU(c, cudaMalloc(&c->wf.list[1], lb));
+            if (!c->wf.ctrl) CU(c, cudaMalloc(&c->wf.ctrl, WF_CTRL_WORDS * sizeof(uint32_t)));
+            c->wf.state_bytes = sb; c->wf.list_bytes = lb;
+        }
+        if (sb != 0) wf = &c->wf;
+    }
     CU(c, cudaEventRecord(c->ev0, stream));
-    RC(c, launch_trace(*p, ex, c->counters_on, stream, c->sm_count, &c->smem_attr_set));
+    RC(c, launch_trace(*p, ex, c->counters_on, stream, c->sm_count, &c->smem_attr_set, wf, &c->launches));
     CU(c, cudaEventRecord(c->ev1, stream));
     c->ev_valid = true;
-    c->launches += 1;
     return 0;
 }
 
@@ -845,6 +866,7 @@ int grtGetAbiLayout(uint64_t out[32]) {
     while (k < 32) out[k++] = 0;
     return 0;
 }
+int grtSetWavefront(grtContext* c, int enable) { if (!c) return 1; c->wavefront = enable != 0; return 0; }
 int grtEnableCounters(grtContext* c, int enable) { if (!c) return 1; c->counters_on = enable != 0; return 0; }
 int grtGetCounters(grtContext* c, grtCounters* out, int reset) {
     if (!c || !out) return 1;
@@ -860,7 +882,7 @@ int grtGetCounters(grtContext* c, grtCounters* out, int reset) {
     for (int k = 0; k < 8; ++k) out->dbg[k] = d.dbg[k];
     out->warp_per_ray_passes = d.warp_per_ray_passes;
     out->warp_composite_rounds = d.warp_composite_rounds; out->warp_loop_iters = d.warp_loop_iters;
-    out->warp_forced_flushes = d.warp_forced_flushes; out->warp_list_full = d.warp_list_full;
+    out->warp_forced_flushes = d.warp_forced_flushes; out->warp_dfs_iters = d.warp_dfs_iters; out->warp_list_full = d.warp_list_full;
     if (reset) CU(c, cudaMemset(c->d_counters, 0, sizeof(DeviceCounters)));
     return 0;
 }

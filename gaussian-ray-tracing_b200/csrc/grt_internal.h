@@ -65,7 +65,7 @@ struct DeviceCounters {
     unsigned long long rays, segments, rounds, hits_gathered, hits_shaded, warp_nodes, warp_leaf_prims, warp_rounds,
         stack_overflow, warp_prims_hit, warp_consume_iters, lanes_repass, order_violations, warp_dfs_fallbacks, warp_candidate_iters;
     unsigned long long dbg[8];  // free-form experiment counters (tools/prof_trace.py prints them)
-    unsigned long long warp_per_ray_passes, warp_composite_rounds, warp_loop_iters, warp_forced_flushes, warp_list_full;
+    unsigned long long warp_per_ray_passes, warp_composite_rounds, warp_loop_iters, warp_forced_flushes, warp_dfs_iters, warp_list_full;
 };
 
 // Extra kernel arguments next to the 144-byte Params.
@@ -87,7 +87,27 @@ struct LaunchExtras {
     // row-band partition of one frame over several GPUs: bands of band_groups 8-row groups; this launch owns the bands b with
     // b % band_stride == band_offset (band_stride <= 1: the whole rectangle)
     uint32_t band_groups, band_stride, band_offset;
+    // wavefront mode (scenes with reflection primitives, trace.cu): payload array, tile lists of this / the next bounce level
+    uint32_t* wf_state;
+    const uint32_t* wf_list_in;
+    uint32_t* wf_list_out;
+    const uint32_t* wf_count_in;
+    uint32_t* wf_count_out;
+    uint32_t wf_level;
+    uint32_t* wf_list_in_w;   // phase 1 with wf_classify: the list it sorts the tiles into (classes 0 / 1), wf_list_out takes class 2
+    uint32_t wf_classify;
 };
+// Device buffers of the wavefront mode, owned by the context and sized for the largest launch rectangle so far.
+constexpr uint32_t WF_MAX_LEVELS = 1056;                 // > TIMEOUT_ITERATIONS + MAX_BOUNCES segments of one ray (tracer.cu:100-104)
+constexpr uint32_t WF_CTRL_WORDS = 3u * WF_MAX_LEVELS + 8u;
+struct WavefrontBuffers {
+    uint32_t* state = nullptr;      // tiles x WF_FIELDS x 32 words
+    uint32_t* list[2] = {nullptr, nullptr};
+    uint32_t* ctrl = nullptr;       // WF_CTRL_WORDS
+    size_t state_bytes = 0, list_bytes = 0;
+};
+size_t wavefront_state_bytes(const LaunchExtras& ex);
+size_t wavefront_list_bytes(const LaunchExtras& ex);
 
 // ---- generic LBVH builder (build.cu) ----
 // Scratch arena of a context: the builder's ~20 temporaries are bump-allocated from one device block that is kept between
@@ -155,6 +175,8 @@ int mesh_gather(const float* d_tri9, const uint2* d_meta, const uint32_t* d_perm
                 cudaStream_t stream, unsigned long long* launches);
 
 // trace kernel (trace.cu)
-int launch_trace(const grtParams& p, const LaunchExtras& ex, bool counters, cudaStream_t stream, int sm_count, bool* smem_attr_set);
+// wf == nullptr (or no primitives): one monolithic launch.  *launches is advanced by the kernels launched.
+int launch_trace(const grtParams& p, const LaunchExtras& ex, bool counters, cudaStream_t stream, int sm_count, bool* smem_attr_set,
+                 const WavefrontBuffers* wf, unsigned long long* launches);
 
 }  // namespace grt

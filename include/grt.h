@@ -93,6 +93,7 @@ typedef struct grtCounters {
     uint64_t warp_composite_rounds; /* compositing rounds (work list + shade + accumulate), per warp */
     uint64_t warp_loop_iters;  /* iterations of the traversal loop, per warp */
     uint64_t warp_forced_flushes; /* flushes that intersected waiting slots behind the frontier because the slots ran out */
+    uint64_t warp_dfs_iters;   /* iterations of the per-ray walk's loop (trace_rays_dfs), per warp */
     uint64_t warp_list_full;   /* record pops that left records in front of the nearest node behind (new-record list full) */
 } grtCounters;
 
@@ -177,6 +178,11 @@ int grtSetDebugOutputs(grtContext* ctx, float* d_rgb32f, uint32_t* d_trace_ids, 
 int grtGetAbiLayout(uint64_t out32[32]);
 int grtEnableCounters(grtContext* ctx, int enable); /* selects the counting kernel variant */
 int grtGetCounters(grtContext* ctx, grtCounters* out, int reset);
+/* Scenes with reflection primitives are traced level by level (wavefront: per bounce one launch for traceMesh + closest hit,
+ * shaders/tracer.cu:155-187, and one for the Gaussian segment, shaders/tracer.cuh:328-394) instead of by one launch that runs
+ * the whole bounce loop of shaders/tracer.cu:58-106, for the first bounce level(s); what is still alive after them finishes in
+ * one more launch.  Same pixels either way; enable = 0 selects the single launch.  Asynchronous like grtLaunch. */
+int grtSetWavefront(grtContext* ctx, int enable);
 int grtGetBuildInfo(grtContext* ctx, grtBuildInfo* out);
 /* Walks the built wide BVH on the host: every live record referenced exactly once, every leaf box inside
  * its ancestors' boxes.  Returns 0 if valid. which: 0 particles, 1 meshes. */

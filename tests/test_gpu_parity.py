@@ -94,6 +94,30 @@ def test_mesh_modes_parity(ctx, grt, orc, mesh_type):
     assert np.abs(no_mesh["rgb32f"] - ora["rgb32f"]).max() > 0.01  # the primitives are actually in view
 
 
+@pytest.mark.parametrize("mesh_type", [0, 1, 2])
+def test_wavefront_equals_single_launch(ctx, grt, mesh_type):
+    """Scenes with primitives are traced level by level (wavefront, the default) or by one launch running the whole bounce loop:
+    the same packets take the same steps either way, so float frame, RGB8 frame and hit-ID sequences are bit-identical."""
+    rec, P, _ = make_scene(grt, 20_000, 104, 192, 128, deg=3, mesh_type=mesh_type)
+    meshes = _config4_meshes(grt)
+    rect, tmax = (0, 40, 192, 48), 160
+    try:
+        ctx.set_wavefront(True)
+        wf = gpu_render(ctx, grt, rec, P, meshes=meshes, trace_rect=rect, trace_max=tmax, counters=True)
+        ctx.set_wavefront(False)
+        mono = gpu_render(ctx, grt, rec, P, meshes=meshes, trace_rect=rect, trace_max=tmax, counters=True)
+    finally:
+        ctx.set_wavefront(True)
+    assert np.array_equal(wf.rgb32f.view(np.uint32), mono.rgb32f.view(np.uint32))
+    assert np.array_equal(wf.rgb8, mono.rgb8)
+    assert np.array_equal(wf.trace_counts, mono.trace_counts) and np.array_equal(wf.trace_ids, mono.trace_ids)
+    for k in ("rays", "segments", "hits_gathered", "hits_shaded", "warp_per_ray_passes"):
+        assert wf.counters[k] == mono.counters[k], k
+    assert wf.counters["stack_overflow"] == 0 and wf.counters["order_violations"] == 0
+    if mesh_type != 1:
+        assert wf.counters["segments"] > wf.counters["rays"]
+
+
 def test_tile_and_batch_equal_full_frame(ctx, grt, orc):
     rec, P, _ = make_scene(grt, 5_000, 105, 100, 70, deg=2)
     full = gpu_render(ctx, grt, rec, P)

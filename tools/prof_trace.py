@@ -29,6 +29,7 @@ def main():
     ap.add_argument("--launches", type=int, default=3)
     ap.add_argument("--no-counters", action="store_true")
     ap.add_argument("--cache", action="store_true")
+    ap.add_argument("--no-wavefront", action="store_true")
     a = ap.parse_args()
     grt = importlib.import_module("gaussian-ray-tracing_b200")
     cache = f"/tmp/grt_scene_{a.n}_{a.seed}.npy"
@@ -39,6 +40,7 @@ def main():
         if a.cache:
             np.save(cache, rec)
     ctx = grt.Context(0)
+    ctx.set_wavefront(not a.no_wavefront)
     ctx.set_particles(rec, 0.01)
     handle, dpart = ctx.build_particle_accel()
     cam = grt.default_camera(rec)

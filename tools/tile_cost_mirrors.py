@@ -8,6 +8,7 @@ grt = importlib.import_module("gaussian-ray-tracing_b200")
 W, H = 1920, 1080
 rec = grt.activate(grt.synth_ply_properties(1_000_000, 1002))
 ctx = grt.Context(0)
+ctx.set_wavefront(False)
 ctx.set_particles(rec, 0.01)
 handle, dpart = ctx.build_particle_accel()
 cam = grt.default_camera(rec)
