@@ -74,7 +74,7 @@ def main():
                                                        "warp_candidate_iters", "warp_composite_rounds", "warp_loop_iters", "warp_forced_flushes", "warp_list_full")}
         d = c.get("dbg", [0] * 8)
         out["per_ray"].update({"inserts": d[0] / rays, "shift_steps": d[1] / rays, "ring_cnt_at_insert": d[2] / max(d[0], 1),
-                               "candidates": d[3] / rays, "proxy_hits": d[4] / rays, "spills": d[5] / rays})
+                               "candidates": d[3] / rays, "proxy_hits": d[4] / rays, "spills": d[5] / rays, "second_face_same_round": d[6] / rays, "second_face_last8": d[7] / rays})
     ms = []
     for _ in range(a.launches):
         ctx.launch(P)
