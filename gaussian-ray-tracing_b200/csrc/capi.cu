@@ -694,7 +694,7 @@ static int do_launch(grtContext* c, cudaStream_t stream, const grtParams* p, uin
     ex.tile_counter = c->d_tile_counter + (size_t)(c->tile_seq++ % TILE_RING) * TILE_SLOT_WORDS;
     CU(c, cudaMemsetAsync(ex.tile_counter, 0, (GRT_SM_REGIONS_HOST ? TILE_SLOT_WORDS : 1u) * sizeof(uint32_t), stream));
     const WavefrontBuffers* wf = nullptr;
-    if (ex.m_count != 0u && c->wavefront) {
+    if (ex.m_count != 0u && c->wavefront && p->type != 1 /* NORMAL: rays end at the primitive, one launch does it */) {
         // wavefront buffers: payload of every pixel of the rectangle + two tile lists, kept between launches, grown when a larger
         // rectangle comes (no allocation on the steady-state path)
         const size_t sb = wavefront_state_bytes(ex), lb = wavefront_list_bytes(ex);
