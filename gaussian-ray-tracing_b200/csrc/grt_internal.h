@@ -137,7 +137,7 @@ struct LbvhResult {
 int lbvh_build(const float4* d_lo, const float4* d_hi, uint32_t n, cudaStream_t stream, LbvhResult* out,
                unsigned long long* launches, BuildScratch* scratch = nullptr);
 int radix_sort_pairs(uint64_t* d_keys, uint64_t* d_keys_tmp, uint32_t* d_vals, uint32_t* d_vals_tmp, uint32_t n,
-                     cudaStream_t stream, unsigned long long* launches, bool* result_in_tmp, BuildScratch* scratch = nullptr);
+                     cudaStream_t stream, unsigned long long* launches, bool* result_in_tmp, BuildScratch* scratch = nullptr, int passes = 8);
 
 // The same sort without any allocation: temporaries in a file-scope device array of build.cu (at most GRT_NOALLOC_SORT_MAX_N pairs;
 // in place; calls that overlap on one GPU race on the array).
