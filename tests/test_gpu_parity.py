@@ -118,6 +118,36 @@ def test_wavefront_equals_single_launch(ctx, grt, mesh_type):
         assert wf.counters["segments"] > wf.counters["rays"]
 
 
+def test_mesh_scene_rows_and_tile_equal_full_frame(ctx, grt):
+    """The sorted two-launch mode numbers its tiles over the launch's own rows / rectangle: row bands (grtLaunchRows) and an aligned
+    tile (grtLaunchTile) of a scene with mirrors reproduce the full frame bit for bit."""
+    W, H = 192, 128
+    rec, P, _ = make_scene(grt, 20_000, 104, W, H, deg=3, mesh_type=0)
+    meshes = _config4_meshes(grt)
+    full = gpu_render(ctx, grt, rec, P, meshes=meshes)
+    part = gpu_render(ctx, grt, rec, P, meshes=meshes, tile=(32, 40, 96, 48))
+    assert np.array_equal(part.rgb8[40:88, 32:128], full.rgb8[40:88, 32:128])
+    assert part.rgb8[:40].max() == 0 and part.rgb8[88:].max() == 0
+    ctx.set_particles(rec, 0.01)
+    P.handle, P.d_particles = ctx.build_particle_accel()
+    ctx.set_meshes(meshes)
+    P.mesh_handle, P.d_meshes = ctx.build_mesh_accel()
+    d = ctx.malloc(W * H * 3)
+    P.output_buffer = d
+    try:
+        for band_rows, G in [(8, 2), (16, 3)]:
+            ctx.memset(d, 0, W * H * 3)
+            for r in range(G):
+                ctx.launch_rows(P, band_rows, G, r)
+            ctx.sync()
+            assert np.array_equal(ctx.to_host(d, (H, W, 3), np.uint8), full.rgb8), (band_rows, G)
+    finally:
+        ctx.free(d)
+        P.output_buffer = None
+        ctx.set_meshes([])
+        ctx.build_mesh_accel()
+
+
 def test_tile_and_batch_equal_full_frame(ctx, grt, orc):
     rec, P, _ = make_scene(grt, 5_000, 105, 100, 70, deg=2)
     full = gpu_render(ctx, grt, rec, P)
