@@ -16,7 +16,8 @@ def main():
     ctx = grt.Context(0)
     sizes = [(100_000, 1001), (1_000_000, 1002), (6_000_000, 1003)]
     if len(sys.argv) > 1:
-        sizes = [s for s in sizes if str(s[0]) in sys.argv[1:]]
+        sel = [a for a in sys.argv[1:] if a.isdigit()]
+        sizes = [s for s in sizes if str(s[0]) in sel] if sel else sizes
     reps = 3 if "--short" in sys.argv else 8
     for n, seed in sizes:
         rec = grt.activate(grt.synth_ply_properties(n, seed))
