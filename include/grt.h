@@ -181,7 +181,9 @@ int grtGetCounters(grtContext* ctx, grtCounters* out, int reset);
 /* Scenes with reflection primitives are traced level by level (wavefront: per bounce one launch for traceMesh + closest hit,
  * shaders/tracer.cu:155-187, and one for the Gaussian segment, shaders/tracer.cuh:328-394) instead of by one launch that runs
  * the whole bounce loop of shaders/tracer.cu:58-106, for the first bounce level(s); what is still alive after them finishes in
- * one more launch.  Same pixels either way; enable = 0 selects the single launch.  Asynchronous like grtLaunch. */
+ * one more launch.  Same pixels either way; enable = 0 selects the single launch.  Asynchronous like grtLaunch.  The per-pixel
+ * payload (30 words per pixel of the launch rectangle) lives in ONE context-owned buffer: launches of a scene with primitives
+ * must not overlap on the GPU (same stream, or ordered by events); scenes without primitives are not affected. */
 int grtSetWavefront(grtContext* ctx, int enable);
 int grtGetBuildInfo(grtContext* ctx, grtBuildInfo* out);
 /* Walks the built wide BVH on the host: every live record referenced exactly once, every leaf box inside
